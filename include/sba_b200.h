@@ -1,0 +1,224 @@
+/*
+ * sba_b200.h -- C ABI of libsba_b200.so, the B200-native (sm_100a, FP64 CUDA)
+ * bundle-adjustment engine that drops in for the hot path of steviapp's
+ * libs/sparsesolver SBA solver.
+ *
+ * Every entry point names the reference interface it replaces (paths relative
+ * to the reference tree, french-paragon/steviapp @ 08eee50c).  Plain pointers
+ * and sizes only; no exception crosses this boundary; every function that can
+ * fail returns an int status (0 = ok, <0 = error, text via sba_last_error).
+ *
+ * There is NO CPU fallback: if no CUDA device is usable sba_create fails with
+ * SBA_ERR_NO_DEVICE.
+ *
+ * Conventions kept from the reference:
+ *   - pose parameter blocks are sensor->world: rAxis[3] (axis-angle, ambient
+ *     R^3, no manifold) and t[3] (PoseNode, libs/sparsesolver/modularsbasolver.h:593-599;
+ *     AddParameterBlock(ptr,3) at modularsbasolver.cpp:837-838);
+ *   - intrinsics per camera model are the five blocks f[1], pp[2], k[3], t[2],
+ *     B[2] in that order (sbamodules/pinholecameraprojectormodule.cpp:112-122),
+ *     10 doubles; B is read but unused and the skew uses t (reference quirk,
+ *     sbamodules/pinholecameraprojectormodule.h:46-47);
+ *   - cost = 1/2 sum r^2 (Ceres convention);
+ *   - parameter arrays stay owned by the caller and are UPDATED IN PLACE by
+ *     sba_solve, as ceres::Solve does with the registered blocks.
+ */
+#ifndef SBA_B200_H
+#define SBA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SBA_INTR_STRIDE 10
+
+/* status codes */
+#define SBA_OK 0
+#define SBA_ERR_NO_DEVICE (-1)
+#define SBA_ERR_CUDA (-2)
+#define SBA_ERR_INVALID (-3)      /* bad argument / call order */
+#define SBA_ERR_EVAL_FAILED (-4)  /* initial point: a plane-cost functor "returned false" (Pbar.z < 0) */
+#define SBA_ERR_NUMERIC (-5)      /* singular point block / non-PD preconditioner block */
+#define SBA_ERR_COMM (-6)         /* NCCL unavailable or failed */
+
+/* cost kinds: UV2ParametrizedXYZCost Flags (costfunctors/modularuvprojection.h:340-457),
+ * selected per solver by the Qt property useSphericalCostPinholeCamProjCost
+ * (sbamodules/pinholecameraprojectormodule.cpp:28,257-271); per camera here so
+ * mixed scenes (BASELINE config 4) run in one problem. */
+#define SBA_COST_PLANE 0
+#define SBA_COST_SPHERICAL 1
+
+/* prior targets: FixedSizeNormalPrior<3,3> on a point (landmarkssbamodule.cpp:171-202)
+ * or on a pose block (imagealignementsbamodule.cpp:256-286) */
+#define SBA_PRIOR_POINT 0
+#define SBA_PRIOR_CAM_R 1
+#define SBA_PRIOR_CAM_T 2
+
+/* Replaces the ModularSBASolver constructor arguments and setters
+ * (modularsbasolver.h:672,876-884) plus the ceres::Solver::Options the
+ * reference fills at modularsbasolver.cpp:897-924; everything it leaves at the
+ * Ceres default is exposed with that default. */
+typedef struct sba_options {
+    int32_t device;               /* CUDA device ordinal; -1 = current device */
+    int32_t max_iterations;       /* setOptimizationSteps */
+    double function_tolerance;    /* setFuncTolerance (1e-8)  */
+    double parameter_tolerance;   /* setParamsTolerance (1e-10) */
+    double gradient_tolerance;    /* Ceres default 1e-10 */
+    double initial_radius;        /* 1e4 */
+    double max_radius;            /* 1e16 */
+    double min_radius;            /* 1e-32 */
+    double min_lm_diagonal;       /* 1e-6 */
+    double max_lm_diagonal;       /* 1e32 */
+    double min_relative_decrease; /* 1e-3 */
+    int32_t jacobi_scaling;       /* 1 */
+    double pcg_rel_tol;           /* relative tolerance of the reduced solve (sqrt(r.z / r0.z0)) */
+    int32_t pcg_max_iters;        /* Ceres max_linear_solver_iterations = 500 */
+    int32_t pcg_check_every;      /* host reads the convergence scalar every n PCG iterations (1 = exact oracle iteration count) */
+    int32_t verbose;
+} sba_options;
+
+#define SBA_MAX_HISTORY 512
+typedef struct sba_summary {
+    int32_t status;               /* 0 = iteration cap, 1 = converged, <0 failure */
+    int32_t iterations;           /* LM iterations executed */
+    int32_t successful_steps;
+    int32_t pcg_iterations_total;
+    double initial_cost, final_cost;
+    double cost_history[SBA_MAX_HISTORY];
+    double radius_history[SBA_MAX_HISTORY];
+    int32_t pcg_iters_history[SBA_MAX_HISTORY];
+    /* device time, CUDA events on the solver's stream, milliseconds */
+    double ms_total;              /* whole LM loop, inputs already in HBM */
+    double ms_linearize;          /* K1 residual+Jacobian launches */
+    double ms_schur;              /* K2 point blocks + camera blocks + preconditioner */
+    double ms_pcg;                /* K3 */
+    double ms_update;             /* K4 back-substitution, update, trial cost */
+    double ms_h2d, ms_d2h;        /* host<->device copies done by sba_solve */
+    int32_t kernel_launches;      /* kernels launched by the last sba_solve */
+} sba_summary;
+
+/* one LM iteration report; replaces ModularSBASolverIterationCallback
+ * (modularsbasolver.cpp:30-56): return 0 to continue, non-zero to abort */
+typedef struct sba_iteration_info {
+    int32_t iteration;
+    double cost, cost_change, radius;
+    int32_t step_valid, step_accepted, pcg_iterations;
+} sba_iteration_info;
+typedef int (*sba_iteration_callback)(const sba_iteration_info*, void* user);
+
+typedef struct sba_solver sba_solver;
+
+void sba_default_options(sba_options* o);
+
+/* ModularSBASolver::ModularSBASolver + init() prologue (modularsbasolver.cpp:679-706) */
+int sba_create(const sba_options* o, sba_solver** out);
+/* ModularSBASolver::cleanup (modularsbasolver.cpp:1091-1143) */
+void sba_destroy(sba_solver* s);
+const char* sba_last_error(const sba_solver* s);
+/* error text for a failed sba_create (no handle yet) */
+const char* sba_create_error(void);
+
+/* Camera models: PinholeCamProjModule::init intrinsic blocks
+ * (sbamodules/pinholecameraprojectormodule.cpp:302-533), held constant
+ * (FixedParameter::CameraInternal, :358-361,406-408). */
+int sba_set_intrinsics(sba_solver* s, int32_t n_models, const double* intr10);
+
+/* Pose blocks: getNodeForFrame + initManagedParameters
+ * (modularsbasolver.cpp:233-306,804-870).  raxis/t are 3*n AoS, caller-owned,
+ * updated in place by sba_solve.  fixed -> SetParameterBlockConstant. */
+int sba_set_poses(sba_solver* s, double* raxis, double* t, int32_t n,
+                  const int32_t* cam_model, const uint8_t* fixed,
+                  const uint8_t* cost_kind);
+
+/* Point blocks: getNodeForLandmark (modularsbasolver.cpp:196-231). */
+int sba_set_points(sba_solver* s, double* xyz, int32_t n, const uint8_t* fixed);
+
+/* Bulk form of ProjectorModule::addProjectionCostFunction
+ * (modularsbasolver.h:169-177; PinholeCamProjModule impl
+ * sbamodules/pinholecameraprojectormodule.cpp:46-272): observation i links
+ * pose cam_idx[i] and point pt_idx[i] with pixel uv[2i..2i+1] and 2x2
+ * stiffness info[4i..4i+3] (row-major; NULL = identity).  May be called
+ * repeatedly; observations accumulate in call order. */
+int sba_add_observations(sba_solver* s, int32_t n, const int32_t* cam_idx,
+                         const int32_t* pt_idx, const double* uv,
+                         const double* info);
+
+/* problem.AddResidualBlock(new FixedSizeNormalPrior<3,3>(A,b), nullptr, ptr)
+ * (costfunctors/fixedsizenormalprior.h:75-112): r = A (x - b), A row-major 3x3. */
+int sba_add_priors(sba_solver* s, int32_t n, const int32_t* kind,
+                   const int32_t* index, const double* A9, const double* b3);
+
+/* End of init(): sorts observations by camera (32-slot aligned segments),
+ * builds the by-point index and uploads everything to HBM.  Called implicitly
+ * by the first evaluate/solve. */
+int sba_finalize(sba_solver* s);
+
+/* Re-upload the caller's current parameter values (warm start semantics of
+ * modularsbasolver.cpp:265-302) / read the device values back. */
+int sba_upload_parameters(sba_solver* s);
+int sba_download_parameters(sba_solver* s);
+
+/* ceres::Problem::Evaluate as the reference tests call it through
+ * ceresProblem() (modularsbasolver.h:856, tests/test_sba_solver/main.cpp:219-234).
+ * Outputs in the caller's observation order, any may be NULL:
+ * residuals 2*n_obs, jac_cam n_obs*2*6 row-major [d/dr | d/dt], jac_pt n_obs*2*3.
+ * Returns SBA_OK, or 1 if some plane observation has Pbar.z < 0 (those rows are 0). */
+int sba_evaluate(sba_solver* s, double* cost, double* residuals,
+                 double* jac_cam, double* jac_pt);
+
+/* Test hooks on the linear algebra (same shapes as the oracle's):
+ * gc 6*n_cams, gp 3*n_pts, Hcc 36*n_cams, Hpp 9*n_pts (undamped). */
+int sba_normal_blocks(sba_solver* s, double* gc, double* gp, double* Hcc, double* Hpp);
+/* y = S x and reduced rhs for explicit damping diagonals lam_c (6*n_cams), lam_p (3*n_pts) */
+int sba_schur_matvec(sba_solver* s, const double* lam_c, const double* lam_p,
+                     const double* x, double* y, double* rhs);
+
+/* ModularSBASolver::opt_step -> ceres::Solve (modularsbasolver.cpp:884-951).
+ * copy_params: 1 = upload the caller's arrays first and write results back
+ * (the reference's observable behaviour); 0 = run on the values already
+ * resident in HBM and leave the result there (sba_download_parameters reads it). */
+int sba_solve(sba_solver* s, int32_t copy_params, sba_summary* summary);
+int sba_set_iteration_callback(sba_solver* s, sba_iteration_callback cb, void* user);
+int sba_set_options(sba_solver* s, const sba_options* o);
+
+/* Kernel-level timing hook for bench.py: runs `reps` back-to-back launches of
+ * one pipeline stage on the resident problem and returns the mean device time
+ * per launch in ms (CUDA events on the solver's stream).
+ * stage: 0 = K1 residual+Jacobian, 1 = K1c cost only, 2 = K2 Schur assembly
+ * (point blocks + camera blocks), 3 = implicit Schur mat-vec, 4 = preconditioner build. */
+int sba_time_stage(sba_solver* s, int32_t stage, int32_t reps, double* ms_per_launch);
+
+/* Batched multi-view DLT triangulation (adjacent to the LM loop; reference has
+ * pairwise forms only: sbainitializer.cpp:987-1063, modularuvprojection.h:741-757).
+ * Uses the poses/intrinsics registered on the handle.  views of point i are
+ * view_off[i]..view_off[i+1]. */
+int sba_triangulate(sba_solver* s, int32_t n_points, const int32_t* view_off,
+                    const int32_t* view_cam, const double* view_uv,
+                    double* xyz_out, uint8_t* ok_out, double* ms_kernel);
+
+/* Multi-GPU (one process per GPU): points and their observations are sharded
+ * by the caller (sba_partition_points), cameras replicated; the library
+ * all-reduces camera blocks, mat-vec partials and scalars with NCCL.
+ * unique_id is a 128-byte ncclUniqueId made by rank 0 (sba_comm_unique_id)
+ * and distributed by the launcher. */
+int sba_comm_unique_id(uint8_t id128[128]);
+int sba_comm_init(sba_solver* s, int32_t rank, int32_t nranks, const uint8_t id128[128]);
+
+/* Host-only helper: contiguous point ranges balanced by observation count.
+ * begin has nranks+1 entries. */
+int sba_partition_points(int32_t n_pts, const int32_t* obs_per_point,
+                         int32_t nranks, int32_t* begin);
+
+/* sizes of the resident problem (after finalize): n_slots is the padded
+ * camera-sorted slot count, n_tiles the warp tiles */
+int sba_problem_sizes(const sba_solver* s, int32_t* n_cams, int32_t* n_pts,
+                      int32_t* n_obs, int32_t* n_slots, int32_t* n_tiles);
+
+const char* sba_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

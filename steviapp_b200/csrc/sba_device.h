@@ -1,0 +1,134 @@
+// sba_device.h -- resident (HBM) data layout of one rank's problem shard and the
+// launch wrappers of sba_kernels.cu.  See DESIGN.md "Data layout in HBM".
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace sba {
+
+constexpr int TILE_SLOTS = 256;      // max observation slots per warp tile (multiple of 32)
+constexpr int WARPS_PER_BLOCK = 8;   // tile kernels: 256 threads
+constexpr int RED_BLOCK = 1024;      // single-block deterministic reductions
+constexpr int PREC = 16;             // doubles per point-order record (128 B = one L2 line)
+constexpr int TP = 28;               // doubles per tile partial
+
+// All arrays are device pointers.  "slot" = position in the camera-sorted,
+// 32-aligned observation order (padding slots have obs_pt = -1 and all-zero J).
+// "pos" = position in the point-sorted order (by-point CSR, no padding).
+//
+// The Jacobian is stored compressed: for every observation
+//   A = d res / d X (2x3)  and  C = d res / d rAxis (2x3);   d res / d t = -A exactly,
+// so Jc = [C | -A], Jp = A.  It is kept twice, once per traversal order:
+//   camera order : SoA planes res[2], C[6], A[6] over slots   (coalesced warp-per-tile passes)
+//   point order  : 128-byte records {A[6], C[6], res[2], pad[2]} over pos (thread-per-point passes)
+struct DevProblem {
+    int32_t Nc, Np, No, Ns, Nt, Nm, Nprior;
+    // cameras (replicated on every rank)
+    double* cam_r;        // 3*Nc AoS (PoseNode::rAxis)
+    double* cam_t;        // 3*Nc AoS
+    double* cam_cache;    // 24*Nc, see sba_math.cuh
+    int32_t* cam_model;   // Nc
+    uint8_t* cam_fixed;   // Nc
+    uint8_t* cam_kind;    // Nc (0 plane, 1 spherical)
+    double* intr;         // 10*Nm
+    // points (this rank's shard), 4 doubles per point (x,y,z,pad): one 32 B sector per gather
+    double* pts;          // 4*Np
+    uint8_t* pt_fixed;    // Np
+    // observations, camera-sorted slots
+    double* obs_uv;       // 2*Ns interleaved (u,v): one 128-bit load per observation
+    int32_t* obs_pt;      // Ns, -1 = padding
+    double* obs_info;     // 4 planes of Ns, or nullptr (identity stiffness)
+    // warp tiles: consecutive slots of one camera, length multiple of 32, <= TILE_SLOTS
+    int32_t* tile_cam;    // Nt
+    int32_t* tile_start;  // Nt
+    int32_t* tile_len;    // Nt
+    int32_t* cam_tile_off;// Nc+1 (tiles of camera c are cam_tile_off[c]..cam_tile_off[c+1])
+    // by-point CSR over pos
+    int32_t* pt_off;      // Np+1
+    int32_t* pos_slot;    // No: slot of the observation at pos
+    int32_t* pos_cam;     // No: camera of the observation at pos
+    double* pos_uv;       // 2*No: (u,v) in point order (static copy)
+    double* pos_info;     // 4*No AoS or nullptr
+    // materialised linearisation
+    double* res;          // 2 planes of Ns
+    double* Cc;           // 6 planes of Ns   (d res / d rAxis)
+    double* Ac;           // 6 planes of Ns   (d res / d X)
+    double* prec;         // PREC*No point-order records
+    // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
+    int32_t Ngroup;
+    int32_t* pg_off;      // Ngroup+1
+    int32_t* pg_kind;     // Ngroup (0 point, 1 cam r, 2 cam t)
+    int32_t* pg_index;    // Ngroup
+    double* prior_A;      // 9*Nprior (sorted by group)
+    double* prior_b;      // 3*Nprior
+    double* prior_res;    // 3*Nprior
+    // normal-equation blocks
+    double* Hpp;          // 8*Np AoS: packed symmetric 3x3 (6) + pad, undamped
+    double* gp;           // 4*Np AoS
+    double* Hinv;         // 8*Np AoS: damped inverse, packed symmetric
+    double* Hcc;          // 21*Nc AoS packed symmetric upper, undamped   } contiguous: one
+    double* gc;           // 6*Nc AoS                                     } all-reduce payload
+    double* Sd;           // 21*Nc AoS: sum_o Jc^T (Jp Hinv Jp^T) Jc  (partial on each rank)
+    double* Minv;         // 36*Nc AoS: inverse of the diagonal blocks of S (SCHUR_JACOBI)
+    double* lam_c;        // 6*Nc
+    double* lam_p;        // 4*Np AoS
+    double* scale_c;      // 6*Nc
+    double* scale_p;      // 4*Np AoS
+    // work vectors
+    double* tile_part;    // TP*Nt tile partials
+    double* tile_cost;    // Nt
+    double* y_p;          // 4*Np AoS point-side temporary of the implicit operator
+    double* dp;           // 4*Np AoS step of the points
+    double* pts_saved;    // 4*Np
+    double* cam_saved;    // 6*Nc
+    double* xz;           // 6*Nc: input vector with fixed cameras zeroed
+    double* pcg_x, *pcg_r, *pcg_z, *pcg_p, *pcg_q, *rhs;   // 6*Nc each
+    double* block_part;   // 4*NB per-block partial sums for scalar reductions over points
+    int32_t NB;           // number of point blocks (ceil(Np/256))
+    double* scalars;      // SC_N doubles
+    int32_t* flags;       // FL_N ints
+};
+
+enum { SC_COST = 0, SC_RZ = 1, SC_RZ0 = 2, SC_PQ = 3, SC_MODEL = 4, SC_STEP2 = 5, SC_X2 = 6, SC_GMAX = 7,
+       SC_COST_OBS = 8, SC_COST_PRIOR = 9, SC_MODEL_PRIOR = 10, SC_N = 32 };
+enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_N = 8 };
+
+// ---- launch wrappers (sba_kernels.cu); all asynchronous on `st` ----
+void launch_pose_cache(const DevProblem& P, cudaStream_t st);
+void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st);   // K1 / K1c, camera order
+void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p: point-order records
+void launch_prior_eval(const DevProblem& P, cudaStream_t st);                    // prior residuals + their cost
+void launch_cost_reduce(const DevProblem& P, cudaStream_t st);                   // tile costs -> SC_COST_OBS
+void launch_point_blocks(const DevProblem& P, cudaStream_t st);                  // K2a: Hpp, gp
+void launch_camera_blocks(const DevProblem& P, cudaStream_t st);                 // K2b: tile partials + per-camera reduce -> Hcc, gc
+void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st);     // add A^T A, A^T r of the priors
+void launch_scaling(const DevProblem& P, int enabled, cudaStream_t st);
+void launch_damping(const DevProblem& P, double radius, double dmin, double dmax, cudaStream_t st);
+void launch_invert_points(const DevProblem& P, cudaStream_t st);
+void launch_schur_diag(const DevProblem& P, cudaStream_t st);                    // -> Sd (partial sum of this rank)
+void launch_schur_diag_invert(const DevProblem& P, cudaStream_t st);             // Minv = (Hcc + lam - Sd)^-1
+// implicit operator pieces.  mode 0: y_p = Hinv * sum Jp^T Jc x ; mode 1: y_p = Hinv gp ;
+// mode 2: dp = -(Hinv (gp + sum Jp^T Jc x))
+void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st);
+// out = hsign * (Hcc x) - sum_o Jc^T Jp y_p  [+ base]; fixed cameras get 0.  Damping is added
+// afterwards (launch_add_damping) so that multi-GPU partials can be all-reduced first.
+void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, double* out,
+                        cudaStream_t st);
+void launch_add_damping(const DevProblem& P, const double* x, double* y, cudaStream_t st);   // y += lam_c .* x
+void launch_zero_fixed(const DevProblem& P, const double* x, double* xz, cudaStream_t st);   // xz = x, 0 at fixed cameras
+void launch_negate(double* x, int n, cudaStream_t st);
+void launch_pcg_init(const DevProblem& P, cudaStream_t st);       // x=0, r=rhs, z=Minv r, p=z, rz, rz0
+void launch_pcg_update(const DevProblem& P, cudaStream_t st);     // alpha, x, r, z, rz, beta, p
+void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st);   // SC_MODEL, SC_STEP2, SC_X2 (local part)
+void launch_apply_step(const DevProblem& P, const double* dc, cudaStream_t st);     // save + x += delta
+void launch_restore(const DevProblem& P, cudaStream_t st);
+void launch_grad_max(const DevProblem& P, cudaStream_t st);
+void launch_gather_outputs(const DevProblem& P, const int32_t* slot_of_obs, double* res_out, double* jc_out,
+                           double* jp_out, cudaStream_t st);
+void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st);
+void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
+void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
+                        const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);
+
+}  // namespace sba

@@ -1,0 +1,243 @@
+// sba_math.cuh -- per-observation / per-block FP64 math of the SBA hot path.
+//
+// Closed-form (not autodiff) derivatives of the reference functor
+//   InvertPose<UV2ParametrizedXYZCost<PinholeUVProjector,Flags,1,2,3,2,2>,0>
+// (sbamodules/pinholecameraprojectormodule.cpp:18-19).  Everything here is
+// __host__ __device__ so that tests/hostmath can compile the SAME expressions
+// with g++ and check them against the oracle without a GPU; the product only
+// ever runs them inside the kernels of sba_kernels.cu.
+#pragma once
+
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define SBA_HD __host__ __device__ __forceinline__
+#else
+#define SBA_HD inline
+#endif
+
+namespace sba {
+
+// camera cache record (doubles): 0..8 Rt = R(r)^T row-major (world->sensor
+// rotation), 9..11 t (sensor->world translation), 12..20 Jr = right Jacobian of
+// SO(3) at r, 21..23 padding (record = 192 B, sector aligned)
+constexpr int CAM_CACHE_STRIDE = 24;
+
+// a = sin(th)/th, b = (1-cos th)/th^2, c = (th - sin th)/th^3 with series near 0.
+SBA_HD void so3_coeffs(double th2, double* a, double* b, double* c) {
+    if (th2 > 1e-4) {
+        const double th = sqrt(th2);
+        double s, co;
+#if defined(__CUDA_ARCH__)
+        sincos(th, &s, &co);
+#else
+        s = sin(th); co = cos(th);
+#endif
+        const double sh = sin(0.5 * th);
+        *a = s / th;
+        *b = 2.0 * sh * sh / th2;            // (1 - cos th)/th^2 without cancellation
+        if (th2 > 0.25) {
+            *c = (th - s) / (th2 * th);
+        } else {
+            // (th - sin th)/th^3 series: cancellation-free below th = 0.5
+            *c = (1.0 / 6.0) * (1.0 - th2 * (1.0 / 20.0) * (1.0 - th2 * (1.0 / 42.0) * (1.0 - th2 * (1.0 / 72.0) *
+                 (1.0 - th2 * (1.0 / 110.0) * (1.0 - th2 * (1.0 / 156.0) * (1.0 - th2 * (1.0 / 210.0)))))));
+        }
+        (void)co;
+    } else {
+        *a = 1.0 - th2 * (1.0 / 6.0) * (1.0 - th2 * (1.0 / 20.0) * (1.0 - th2 * (1.0 / 42.0)));
+        *b = 0.5 * (1.0 - th2 * (1.0 / 12.0) * (1.0 - th2 * (1.0 / 30.0) * (1.0 - th2 * (1.0 / 56.0))));
+        *c = (1.0 / 6.0) * (1.0 - th2 * (1.0 / 20.0) * (1.0 - th2 * (1.0 / 42.0) * (1.0 - th2 * (1.0 / 72.0))));
+    }
+}
+
+// K0: per-camera cache.  Parameters (r,t) are sensor->world; InvertPose
+// (costfunctors/posedecoratorfunctors.h:1106-1155) hands the functor
+// (r',t') = (-r, -R(-r)t), so Pbar = R(r)^T (X - t)  (modularuvprojection.h:389-394).
+//   R(r)   = I + a [r]x + b [r]x^2
+//   dPbar/dr = [Pbar]x Jr(r),  Jr(r) = I - b [r]x + c [r]x^2   (right Jacobian of SO(3);
+//   equals the Gallego-Yezzi closed form (r r^T - (R - I)[r]x)/|r|^2 premultiplied by R^T)
+SBA_HD void pose_cache(const double* r, const double* t, double* out) {
+    const double x = r[0], y = r[1], z = r[2];
+    const double th2 = x * x + y * y + z * z;
+    double a, b, c;
+    so3_coeffs(th2, &a, &b, &c);
+    // [r]x^2 = r r^T - th2 I
+    const double xx = x * x - th2, yy = y * y - th2, zz = z * z - th2;
+    const double xy = x * y, xz = x * z, yz = y * z;
+    // R = I + a K + b K2, K = [r]x = [[0,-z,y],[z,0,-x],[-y,x,0]];  store R^T
+    const double R00 = 1.0 + b * xx, R01 = -a * z + b * xy, R02 = a * y + b * xz;
+    const double R10 = a * z + b * xy, R11 = 1.0 + b * yy, R12 = -a * x + b * yz;
+    const double R20 = -a * y + b * xz, R21 = a * x + b * yz, R22 = 1.0 + b * zz;
+    out[0] = R00; out[1] = R10; out[2] = R20;
+    out[3] = R01; out[4] = R11; out[5] = R21;
+    out[6] = R02; out[7] = R12; out[8] = R22;
+    out[9] = t[0]; out[10] = t[1]; out[11] = t[2];
+    // Jr = I - b K + c K2
+    out[12] = 1.0 + c * xx; out[13] = b * z + c * xy;  out[14] = -b * y + c * xz;
+    out[15] = -b * z + c * xy; out[16] = 1.0 + c * yy; out[17] = b * x + c * yz;
+    out[18] = b * y + c * xz;  out[19] = -b * x + c * yz; out[20] = 1.0 + c * zz;
+    out[21] = 0.0; out[22] = 0.0; out[23] = 0.0;
+}
+
+// PinholeUVProjector::dirFromUV (sbamodules/pinholecameraprojectormodule.h:28-71)
+// intr = f, pp[2], k[3], t[2], B[2]; skew built from t (":46-47"), B unused.
+SBA_HD void dir_from_uv(double u, double v, const double* in, double* d) {
+    const double f = in[0];
+    const double y = (v - in[2]) / f;
+    const double x = (u - in[1] - in[7] * y) / (f + in[6]);
+    const double r2 = x * x + y * y;
+    const double rad = r2 * (in[3] + r2 * (in[4] + r2 * in[5]));
+    const double xy = x * y;
+    const double dtx = 2.0 * xy * in[6] + (r2 + 2.0 * x * x) * in[7];
+    const double dty = (r2 + 2.0 * y * y) * in[6] + 2.0 * xy * in[7];
+    d[0] = (x + x * rad + dtx) * f;
+    d[1] = (y + y * rad + dty) * f;
+    d[2] = f;
+}
+
+// One observation.  cc = camera cache record, X = point, d = view ray,
+// W = 2x2 stiffness (row-major) or nullptr (identity).
+// Outputs: res[2]; if JAC: Jc[12] = rows [d/dr(3) d/dt(3)], Jp[6] = rows d/dX(3).
+// Returns false when the plane cost sees Pbar.z < 0 (modularuvprojection.h:395-399).
+template <bool JAC>
+SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const double* W,
+                     int spherical, double* res, double* Jc, double* Jp) {
+    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
+    const double Px = cc[0] * vx + cc[1] * vy + cc[2] * vz;
+    const double Py = cc[3] * vx + cc[4] * vy + cc[5] * vz;
+    const double Pz = cc[6] * vx + cc[7] * vy + cc[8] * vz;
+    double e0, e1;
+    // Pi = d e / d Pbar, rows (p00, 0, p02), (0, p11, p12)
+    double p00, p02, p11, p12;
+    if (!spherical) {
+        if (Pz < 0.0) return false;
+        const double iz = 1.0 / Pz;
+        const double px = Px * iz, py = Py * iz;
+        e0 = px * d[2] - d[0];                       // ":414-416"
+        e1 = py * d[2] - d[1];
+        if (JAC) {
+            const double s = d[2] * iz;
+            p00 = s; p11 = s; p02 = -s * px; p12 = -s * py;
+        }
+    } else {
+        // ":417-432": alpha1 = atan2(dx,dz), rotate (Pz,Px) by alpha1, angle of the result,
+        // scaled by |(dx,dz)| / cos(alpha1) = (dx^2+dz^2)/dz.
+        const double nx2 = d[0] * d[0] + d[2] * d[2], ny2 = d[1] * d[1] + d[2] * d[2];
+        const double inx = 1.0 / sqrt(nx2), iny = 1.0 / sqrt(ny2);
+        const double cx = d[2] * inx, sx = d[0] * inx;
+        const double cy = d[2] * iny, sy = d[1] * iny;
+        const double kx = nx2 / d[2], ky = ny2 / d[2];
+        const double a0 = cx * Pz + sx * Px, a1 = cx * Px - sx * Pz;
+        const double b0 = cy * Pz + sy * Py, b1 = cy * Py - sy * Pz;
+        e0 = atan2(a1, a0) * kx;
+        e1 = atan2(b1, b0) * ky;
+        if (JAC) {
+            const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
+            p00 = qx * Pz; p02 = -qx * Px;
+            p11 = qy * Pz; p12 = -qy * Py;
+        }
+    }
+    if (W) {
+        res[0] = W[0] * e0 + W[1] * e1;
+        res[1] = W[2] * e0 + W[3] * e1;
+    } else {
+        res[0] = e0; res[1] = e1;
+    }
+    if (JAC) {
+        // A = Pi * Rt (2x3) = d e / d X ; d e / d t = -A
+        double A[6];
+        A[0] = p00 * cc[0] + p02 * cc[6]; A[1] = p00 * cc[1] + p02 * cc[7]; A[2] = p00 * cc[2] + p02 * cc[8];
+        A[3] = p11 * cc[3] + p12 * cc[6]; A[4] = p11 * cc[4] + p12 * cc[7]; A[5] = p11 * cc[5] + p12 * cc[8];
+        // B = Pi * [Pbar]x (2x3)
+        const double B0 = -p02 * Py, B1 = -p00 * Pz + p02 * Px, B2 = p00 * Py;
+        const double B3 = p11 * Pz - p12 * Py, B4 = p12 * Px, B5 = -p11 * Px;
+        // C = B * Jr (2x3) = d e / d r
+        double C[6];
+        C[0] = B0 * cc[12] + B1 * cc[15] + B2 * cc[18];
+        C[1] = B0 * cc[13] + B1 * cc[16] + B2 * cc[19];
+        C[2] = B0 * cc[14] + B1 * cc[17] + B2 * cc[20];
+        C[3] = B3 * cc[12] + B4 * cc[15] + B5 * cc[18];
+        C[4] = B3 * cc[13] + B4 * cc[16] + B5 * cc[19];
+        C[5] = B3 * cc[14] + B4 * cc[17] + B5 * cc[20];
+        if (W) {
+            for (int j = 0; j < 3; j++) {
+                const double c0 = C[j], c1 = C[3 + j], a0 = A[j], a1 = A[3 + j];
+                Jc[j] = W[0] * c0 + W[1] * c1;       Jc[6 + j] = W[2] * c0 + W[3] * c1;
+                const double x0 = W[0] * a0 + W[1] * a1, x1 = W[2] * a0 + W[3] * a1;
+                Jp[j] = x0; Jp[3 + j] = x1;
+                Jc[3 + j] = -x0; Jc[9 + j] = -x1;
+            }
+        } else {
+            for (int j = 0; j < 3; j++) {
+                Jc[j] = C[j]; Jc[6 + j] = C[3 + j];
+                Jp[j] = A[j]; Jp[3 + j] = A[3 + j];
+                Jc[3 + j] = -A[j]; Jc[9 + j] = -A[3 + j];
+            }
+        }
+    }
+    return true;
+}
+
+// symmetric 3x3 inverse by adjugate; H = (h00,h01,h02,h11,h12,h22) -> same packing.
+// Returns false if the determinant is 0 or not finite.
+SBA_HD bool inv3_sym(const double* H, double* Hi) {
+    const double a = H[0], b = H[1], c = H[2], d = H[3], e = H[4], f = H[5];
+    const double C00 = d * f - e * e, C01 = c * e - b * f, C02 = b * e - c * d;
+    const double det = a * C00 + b * C01 + c * C02;
+    if (!(fabs(det) > 0.0) || !isfinite(det)) return false;
+    const double id = 1.0 / det;
+    Hi[0] = C00 * id; Hi[1] = C01 * id; Hi[2] = C02 * id;
+    Hi[3] = (a * f - c * c) * id; Hi[4] = (b * c - a * e) * id; Hi[5] = (a * d - b * b) * id;
+    return true;
+}
+
+// packed upper-triangular index of a symmetric 6x6 (21 entries, row-major upper)
+SBA_HD int sym6(int i, int j) {
+    if (i > j) { const int t = i; i = j; j = t; }
+    return i * 6 - (i * (i - 1)) / 2 + (j - i);
+}
+
+// inverse of an SPD 6x6 (full row-major in/out) by Cholesky; false if not PD
+SBA_HD bool inv6_spd(const double* A, double* Ai) {
+    double L[36];
+    for (int i = 0; i < 36; i++) L[i] = A[i];
+    for (int j = 0; j < 6; j++) {
+        double dd = L[j * 6 + j];
+        for (int k = 0; k < j; k++) dd -= L[j * 6 + k] * L[j * 6 + k];
+        if (!(dd > 0.0)) return false;
+        dd = sqrt(dd);
+        L[j * 6 + j] = dd;
+        for (int i = j + 1; i < 6; i++) {
+            double s = L[i * 6 + j];
+            for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k];
+            L[i * 6 + j] = s / dd;
+        }
+    }
+    for (int j = 0; j < 6; j++) {
+        double e[6];
+        for (int i = 0; i < 6; i++) e[i] = (i == j) ? 1.0 : 0.0;
+        for (int i = 0; i < 6; i++) { double s = e[i]; for (int k = 0; k < i; k++) s -= L[i * 6 + k] * e[k]; e[i] = s / L[i * 6 + i]; }
+        for (int i = 5; i >= 0; i--) { double s = e[i]; for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * e[k]; e[i] = s / L[i * 6 + i]; }
+        for (int i = 0; i < 6; i++) Ai[i * 6 + j] = e[i];
+    }
+    return true;
+}
+
+// One DLT view: accumulates the inhomogeneous normal equations of the two rows
+//   (x r3 - r1) . X = x c3 - c1,  (y r3 - r2) . X = y c3 - c2
+// (r_i rows of R^T, c = R^T t, (x,y) = dirFromUV.xy / dir.z).  A packed sym 3x3.
+SBA_HD void dlt_accumulate(const double* cc, const double* d, double* A, double* b) {
+    const double x = d[0] / d[2], y = d[1] / d[2];
+    const double c0 = cc[0] * cc[9] + cc[1] * cc[10] + cc[2] * cc[11];
+    const double c1 = cc[3] * cc[9] + cc[4] * cc[10] + cc[5] * cc[11];
+    const double c2 = cc[6] * cc[9] + cc[7] * cc[10] + cc[8] * cc[11];
+    const double r0x = x * cc[6] - cc[0], r0y = x * cc[7] - cc[1], r0z = x * cc[8] - cc[2];
+    const double r1x = y * cc[6] - cc[3], r1y = y * cc[7] - cc[4], r1z = y * cc[8] - cc[5];
+    const double h0 = x * c2 - c0, h1 = y * c2 - c1;
+    b[0] += r0x * h0 + r1x * h1; b[1] += r0y * h0 + r1y * h1; b[2] += r0z * h0 + r1z * h1;
+    A[0] += r0x * r0x + r1x * r1x; A[1] += r0x * r0y + r1x * r1y; A[2] += r0x * r0z + r1x * r1z;
+    A[3] += r0y * r0y + r1y * r1y; A[4] += r0y * r0z + r1y * r1z; A[5] += r0z * r0z + r1z * r1z;
+}
+
+}  // namespace sba
