@@ -91,8 +91,9 @@ struct DevProblem {
 };
 
 enum { SC_COST = 0, SC_RZ = 1, SC_RZ0 = 2, SC_PQ = 3, SC_MODEL = 4, SC_STEP2 = 5, SC_X2 = 6, SC_GMAX = 7,
-       SC_COST_OBS = 8, SC_COST_PRIOR = 9, SC_MODEL_PRIOR = 10, SC_N = 32 };
-enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_N = 8 };
+       SC_COST_OBS = 8, SC_COST_PRIOR = 9, SC_MODEL_PRIOR = 10, SC_COST_PRIOR_CAM = 11, SC_MODEL_PRIOR_CAM = 12,
+       SC_STEP2_CAM = 13, SC_X2_CAM = 14, SC_GMAX_CAM = 15, SC_N = 32 };
+enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, FL_N = 8 };
 
 // ---- launch wrappers (sba_kernels.cu); all asynchronous on `st` ----
 void launch_pose_cache(const DevProblem& P, cudaStream_t st);
@@ -111,21 +112,24 @@ void launch_schur_diag_invert(const DevProblem& P, cudaStream_t st);            
 // implicit operator pieces.  mode 0: y_p = Hinv * sum Jp^T Jc x ; mode 1: y_p = Hinv gp ;
 // mode 2: dp = -(Hinv (gp + sum Jp^T Jc x))
 void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st);
-// out = hsign * (Hcc x) - sum_o Jc^T Jp y_p  [+ base]; fixed cameras get 0.  Damping is added
-// afterwards (launch_add_damping) so that multi-GPU partials can be all-reduced first.
-void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, double* out,
-                        cudaStream_t st);
-void launch_add_damping(const DevProblem& P, const double* x, double* y, cudaStream_t st);   // y += lam_c .* x
+// out = -sum_o Jc^T Jp y_p (fixed cameras: 0); if finish: out += hsign * (Hcc x) + damp * lam_c .* x + base.
+// Multi-GPU runs all-reduce the partial first and call launch_camera_finish afterwards.
+void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, int damp, int finish,
+                        double* out, cudaStream_t st);
+void launch_camera_finish(const DevProblem& P, const double* x, const double* base, double hsign, int damp, double* out,
+                          cudaStream_t st);
 void launch_zero_fixed(const DevProblem& P, const double* x, double* xz, cudaStream_t st);   // xz = x, 0 at fixed cameras
 void launch_negate(double* x, int n, cudaStream_t st);
 void launch_pcg_init(const DevProblem& P, cudaStream_t st);       // x=0, r=rhs, z=Minv r, p=z, rz, rz0
-void launch_pcg_update(const DevProblem& P, cudaStream_t st);     // alpha, x, r, z, rz, beta, p
+void launch_pcg_update(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z, rz, beta, p (frozen once converged)
 void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st);   // SC_MODEL, SC_STEP2, SC_X2 (local part)
 void launch_apply_step(const DevProblem& P, const double* dc, cudaStream_t st);     // save + x += delta
 void launch_restore(const DevProblem& P, cudaStream_t st);
 void launch_grad_max(const DevProblem& P, cudaStream_t st);
 void launch_gather_outputs(const DevProblem& P, const int32_t* slot_of_obs, double* res_out, double* jc_out,
                            double* jp_out, cudaStream_t st);
+void launch_unpack_blocks(const DevProblem& P, double* Hcc36, double* Hpp9, double* gp3, cudaStream_t st);
+void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* lam_p3, cudaStream_t st);
 void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st);
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,

@@ -1,0 +1,166 @@
+// sba_kernels.cu -- hand-written sm_100a FP64 kernels of the SBA hot path.
+//
+// All reductions are deterministic: fixed-shape warp-shuffle trees inside a
+// warp tile, fixed-order sums over the tiles of a camera, single-block trees
+// for scalars.  No floating-point atomics anywhere (integer flag stores only).
+//
+// Reference arithmetic restated (closed form instead of autodiff):
+//   K1/K1p : InvertPose<UV2ParametrizedXYZCost<PinholeUVProjector,..>>  (sbamodules/
+//            pinholecameraprojectormodule.cpp:18-19, costfunctors/modularuvprojection.h:368-448)
+//   K2..K4 : the Schur elimination / SCHUR_JACOBI PCG / back-substitution that ceres::Solve
+//            performs for the reference (modularsbasolver.cpp:938); in-tree analogue
+//            modules/g2o/g2o/core/block_solver.hpp:329-479, solvers/pcg/linear_solver_pcg.hpp:84-165
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+// ---------------------------------------------------------------------------
+// K0 pose cache: thread per camera
+// ---------------------------------------------------------------------------
+__global__ void k_pose_cache(DevProblem P) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.Nc) return;
+    double out[CAM_CACHE_STRIDE];
+    pose_cache(P.cam_r + 3 * c, P.cam_t + 3 * c, out);
+#pragma unroll
+    for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
+}
+void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
+    k_pose_cache<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);
+}
+
+// ---------------------------------------------------------------------------
+// K1 residual + Jacobian, camera order.  One warp per tile (<= 256 consecutive
+// slots of ONE camera): camera cache record and intrinsics staged in shared
+// memory once per tile, (u,v) fetched with one 128-bit load per observation,
+// the point with two 128-bit loads (one 32 B sector), outputs written as
+// coalesced SoA planes.  JAC=false is the cost-only variant K1c (trial steps).
+// Algorithmic bytes per observation: in 16 (uv) + 4 (pt); out 16 (res) + 48 (C)
+// + 48 (A) = 132 (+4 B/obs index) -- the "136 B/obs" form of SURVEY 8(d)
+// (J_t = -J_X not stored; 184 B/obs with it).
+// ---------------------------------------------------------------------------
+template <bool JAC>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_residual_jacobian(DevProblem P) {
+    __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
+    if (tile >= P.Nt) return;
+    const int cam = __ldg(P.tile_cam + tile);
+    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    double* cc = s_cam[warp];
+    if (lane < CAM_CACHE_STRIDE) cc[lane] = __ldg(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam + lane);
+    if (lane < 10) cc[CAM_CACHE_STRIDE + lane] = __ldg(P.intr + 10 * __ldg(P.cam_model + cam) + lane);
+    __syncwarp();
+    const double* intr = cc + CAM_CACHE_STRIDE;
+    const int spherical = P.cam_kind[cam];
+    const size_t Ns = (size_t)P.Ns;
+    double acc = 0.0;
+    int bad = 0;
+    for (int s = start + lane; s < start + len; s += 32) {
+        const int pt = __ldg(P.obs_pt + s);
+        if (pt < 0) continue;   // padding slot: planes stay zero
+        const double2 uv = ldg2(P.obs_uv + 2 * (size_t)s);
+        const double2 x01 = ldg2(P.pts + 4 * (size_t)pt), x23 = ldg2(P.pts + 4 * (size_t)pt + 2);
+        const double X[3] = {x01.x, x01.y, x23.x};
+        double d[3];
+        dir_from_uv(uv.x, uv.y, intr, d);
+        double W[4];
+        const double* Wp = nullptr;
+        if (P.obs_info) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) W[i] = __ldg(P.obs_info + i * Ns + s);
+            Wp = W;
+        }
+        double r[2] = {0.0, 0.0}, Jc[12], Jp[6];
+        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp);
+        if (!ok) {
+            bad = 1;
+            r[0] = r[1] = 0.0;
+            if (JAC) {
+#pragma unroll
+                for (int i = 0; i < 12; i++) Jc[i] = 0.0;
+#pragma unroll
+                for (int i = 0; i < 6; i++) Jp[i] = 0.0;
+            }
+        }
+        acc += r[0] * r[0] + r[1] * r[1];
+        if (JAC) {
+            P.res[s] = r[0];
+            P.res[Ns + s] = r[1];
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                P.Cc[(size_t)j * Ns + s] = Jc[j];
+                P.Cc[(size_t)(3 + j) * Ns + s] = Jc[6 + j];
+                P.Ac[(size_t)j * Ns + s] = Jp[j];
+                P.Ac[(size_t)(3 + j) * Ns + s] = Jp[3 + j];
+            }
+        }
+    }
+    acc = warp_sum(acc);
+    bad = __any_sync(FULL, bad);
+    if (lane == 0) {
+        P.tile_cost[tile] = acc;
+        if (bad) P.flags[FL_CHEIRALITY] = 1;
+    }
+}
+void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st) {
+    if (P.Nt == 0) return;
+    const int nb = cdiv(P.Nt, WARPS_PER_BLOCK);
+    if (jac) k_residual_jacobian<true><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    else k_residual_jacobian<false><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
+}
+
+// ---------------------------------------------------------------------------
+// K1p linearisation in point order: thread per point walks its CSR row, rebuilds
+// the same A, C, res (bitwise the same expressions as K1) and writes one 128-byte
+// record per observation.  In: 16 (uv) + 4 (cam) per obs, 32 per point; out 112
+// useful bytes per obs (128 allocated).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_linearize_points(DevProblem P) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.Np) return;
+    const double2 x01 = ldg2(P.pts + 4 * (size_t)p), x23 = ldg2(P.pts + 4 * (size_t)p + 2);
+    const double X[3] = {x01.x, x01.y, x23.x};
+    const int k0 = __ldg(P.pt_off + p), k1 = __ldg(P.pt_off + p + 1);
+    for (int k = k0; k < k1; k++) {
+        const int cam = __ldg(P.pos_cam + k);
+        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+        double ccr[21];
+#pragma unroll
+        for (int i = 0; i < 10; i++) { const double2 v = ldg2(cc + 2 * i); ccr[2 * i] = v.x; ccr[2 * i + 1] = v.y; }
+        ccr[20] = __ldg(cc + 20);
+        const double* in = P.intr + 10 * __ldg(P.cam_model + cam);
+        double intr[10];
+#pragma unroll
+        for (int i = 0; i < 5; i++) { const double2 v = ldg2(in + 2 * i); intr[2 * i] = v.x; intr[2 * i + 1] = v.y; }
+        const double2 uv = ldg2(P.pos_uv + 2 * (size_t)k);
+        double d[3];
+        dir_from_uv(uv.x, uv.y, intr, d);
+        double W[4];
+        const double* Wp = nullptr;
+        if (P.pos_info) {
+            const double2 w01 = ldg2(P.pos_info + 4 * (size_t)k), w23 = ldg2(P.pos_info + 4 * (size_t)k + 2);
+            W[0] = w01.x; W[1] = w01.y; W[2] = w23.x; W[3] = w23.y;
+            Wp = W;
+        }
+        double r[2] = {0.0, 0.0}, Jc[12], Jp[6];
+        const bool ok = obs_eval<true>(ccr, X, d, Wp, P.cam_kind[cam], r, Jc, Jp);
+        if (!ok) {
+            r[0] = r[1] = 0.0;
+#pragma unroll
+            for (int i = 0; i < 12; i++) Jc[i] = 0.0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) Jp[i] = 0.0;
+        }
+        double* rec = P.prec + (size_t)PREC * k;
+        st2(rec + 0, Jp[0], Jp[1]); st2(rec + 2, Jp[2], Jp[3]); st2(rec + 4, Jp[4], Jp[5]);
+        st2(rec + 6, Jc[0], Jc[1]); st2(rec + 8, Jc[2], Jc[6]); st2(rec + 10, Jc[7], Jc[8]);
+        st2(rec + 12, r[0], r[1]);
+    }
+}
+void launch_linearize_points(const DevProblem& P, cudaStream_t st) {
+    if (P.Np == 0) return;
+    k_linearize_points<<<cdiv(P.Np, 256), 256, 0, st>>>(P);
+}
+
+}  // namespace sba

@@ -1,0 +1,196 @@
+// sba_kernels_pcg.cu -- K3 block-Jacobi (SCHUR_JACOBI) preconditioned CG vector
+// updates, K4 step application / model cost change / norms, output gathers and
+// the batched DLT triangulation (K5).
+//
+// PCG follows the loop ceres::Solve runs for ITERATIVE_SCHUR behind
+// modularsbasolver.cpp:938; in-tree analogue modules/g2o/g2o/solvers/pcg/linear_solver_pcg.hpp:84-165.
+// The 6*Nc vectors are tiny (85 KB for 1778 cameras), so each update is ONE
+// single-block kernel: every dot product is a fixed-shape tree, bitwise
+// reproducible, and identical on every rank of a multi-GPU run.
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+__device__ __forceinline__ double minv_row(const DevProblem& P, const double* r, int i) {
+    const int c = i / 6, a = i - 6 * c;
+    const double* M = P.Minv + 36 * (size_t)c + 6 * a;
+    const double* rc = r + 6 * (size_t)c;
+    double v = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; b++) v += M[b] * rc[b];
+    return v;
+}
+
+// x = 0, r = rhs, z = Minv r, p = z, rz = r.z, rz0 = rz, iteration counter = 0
+__global__ void __launch_bounds__(RED_BLOCK) k_pcg_init(DevProblem P) {
+    __shared__ double sh[33];
+    const int n = 6 * P.Nc;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double z = minv_row(P, P.rhs, i);
+        const double r = P.rhs[i];
+        P.pcg_x[i] = 0.0; P.pcg_r[i] = r; P.pcg_z[i] = z; P.pcg_p[i] = z;
+        acc += r * z;
+    }
+    acc = block_sum(acc, sh);
+    if (threadIdx.x == 0) { P.scalars[SC_RZ] = acc; P.scalars[SC_RZ0] = acc; P.flags[FL_PCG_ITERS] = 0; }
+}
+void launch_pcg_init(const DevProblem& P, cudaStream_t st) { k_pcg_init<<<1, RED_BLOCK, 0, st>>>(P); }
+
+// one CG update given q = S p.  Frozen (no state change) once rz <= tol^2 rz0 or the
+// iteration cap is reached, so the host may launch iterations in batches and still stop
+// at exactly the iteration the sequential loop would.
+__global__ void __launch_bounds__(RED_BLOCK) k_pcg_update(DevProblem P, double tol2, int max_iters) {
+    __shared__ double sh[33];
+    const int n = 6 * P.Nc;
+    const double rz = P.scalars[SC_RZ], rz0 = P.scalars[SC_RZ0];
+    const int it = P.flags[FL_PCG_ITERS];
+    if (!(rz > tol2 * rz0) || !(rz0 > 0.0) || it >= max_iters) return;   // uniform across the block
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) acc += P.pcg_p[i] * P.pcg_q[i];
+    const double pq = block_sum(acc, sh);
+    const double alpha = rz / pq;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        P.pcg_x[i] += alpha * P.pcg_p[i];
+        P.pcg_r[i] -= alpha * P.pcg_q[i];
+    }
+    __syncthreads();
+    acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double z = minv_row(P, P.pcg_r, i);
+        P.pcg_z[i] = z;
+        acc += P.pcg_r[i] * z;
+    }
+    const double rz_new = block_sum(acc, sh);
+    const double beta = rz_new / rz;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) P.pcg_p[i] = P.pcg_z[i] + beta * P.pcg_p[i];
+    if (threadIdx.x == 0) { P.scalars[SC_RZ] = rz_new; P.scalars[SC_PQ] = pq; P.flags[FL_PCG_ITERS] = it + 1; }
+}
+void launch_pcg_update(const DevProblem& P, double tol2, int max_iters, cudaStream_t st) {
+    k_pcg_update<<<1, RED_BLOCK, 0, st>>>(P, tol2, max_iters);
+}
+
+// ---------------------------------------------------------------------------
+// K4: model cost change  -sum_o m.(res + m/2),  m = Jc dc + Jp dp
+// (Ceres TrustRegionMinimizer model_cost_change).  Warp per tile, tile partial
+// into tile_cost (free between the linear solve and the trial evaluation).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem P, const double* __restrict__ dc) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
+    if (tile >= P.Nt) return;
+    const int cam = __ldg(P.tile_cam + tile);
+    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    const size_t Ns = (size_t)P.Ns;
+    double x[6];
+#pragma unroll
+    for (int a = 0; a < 6; a++) x[a] = dc[6 * (size_t)cam + a];
+    double acc = 0.0;
+    for (int s = start + lane; s < start + len; s += 32) {
+        const int pt = __ldg(P.obs_pt + s);
+        if (pt < 0) continue;
+        const double2 d01 = ldg2(P.dp + 4 * (size_t)pt), d23 = ldg2(P.dp + 4 * (size_t)pt + 2);
+        double m0 = 0.0, m1 = 0.0;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const double A0 = __ldg(P.Ac + (size_t)a * Ns + s), A1 = __ldg(P.Ac + (size_t)(3 + a) * Ns + s);
+            const double C0 = __ldg(P.Cc + (size_t)a * Ns + s), C1 = __ldg(P.Cc + (size_t)(3 + a) * Ns + s);
+            const double dpa = a == 0 ? d01.x : (a == 1 ? d01.y : d23.x);
+            m0 += C0 * x[a] + A0 * (dpa - x[3 + a]);
+            m1 += C1 * x[a] + A1 * (dpa - x[3 + a]);
+        }
+        const double r0 = __ldg(P.res + s), r1 = __ldg(P.res + Ns + s);
+        acc += m0 * (r0 + 0.5 * m0) + m1 * (r1 + 0.5 * m1);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) P.tile_cost[tile] = acc;
+}
+
+// per-block partials over points: [0] sum dp^2, [1] sum X^2 (free points), [2] max |gp|
+__global__ void __launch_bounds__(256) k_point_stats(DevProblem P) {
+    __shared__ double sh[33];
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    double s2 = 0.0, x2 = 0.0, gm = 0.0;
+    if (p < P.Np && !P.pt_fixed[p]) {
+        const double* d = P.dp + 4 * (size_t)p;
+        const double* X = P.pts + 4 * (size_t)p;
+        const double* g = P.gp + 4 * (size_t)p;
+        s2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+        x2 = X[0] * X[0] + X[1] * X[1] + X[2] * X[2];
+        gm = fmax(fabs(g[0]), fmax(fabs(g[1]), fabs(g[2])));
+    }
+    s2 = block_sum(s2, sh);
+    x2 = block_sum(x2, sh);
+    gm = block_max(gm, sh);
+    if (threadIdx.x == 0) {
+        P.block_part[4 * (size_t)blockIdx.x] = s2;
+        P.block_part[4 * (size_t)blockIdx.x + 1] = x2;
+        P.block_part[4 * (size_t)blockIdx.x + 2] = gm;
+    }
+}
+
+// single block: folds the tile / block partials and the camera + prior parts into scalars.
+//  SC_MODEL      = -(obs part + point-prior part)       (local to this rank)
+//  SC_MODEL_PRIOR_CAM = -(camera-prior part)            (replicated)
+//  SC_STEP2 / SC_X2   = point parts (local);  SC_STEP2_CAM / SC_X2_CAM = camera parts (replicated)
+__global__ void __launch_bounds__(RED_BLOCK) k_model_reduce(DevProblem P, const double* __restrict__ dc) {
+    __shared__ double sh[33];
+    double acc = 0.0;
+    for (int t = threadIdx.x; t < P.Nt; t += blockDim.x) acc += P.tile_cost[t];
+    double mp = 0.0, mc = 0.0;
+    for (int g = threadIdx.x; g < P.Ngroup; g += blockDim.x) {
+        const int kind = P.pg_kind[g], idx = P.pg_index[g];
+        if (kind == 0 ? P.pt_fixed[idx] : P.cam_fixed[idx]) continue;
+        const double* d = kind == 0 ? P.dp + 4 * (size_t)idx : (kind == 1 ? dc + 6 * (size_t)idx : dc + 6 * (size_t)idx + 3);
+        double v = 0.0;
+        for (int i = P.pg_off[g]; i < P.pg_off[g + 1]; i++) {
+            const double* A = P.prior_A + 9 * (size_t)i;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const double m = A[3 * k] * d[0] + A[3 * k + 1] * d[1] + A[3 * k + 2] * d[2];
+                v += m * (P.prior_res[3 * (size_t)i + k] + 0.5 * m);
+            }
+        }
+        if (kind == 0) mp += v; else mc += v;
+    }
+    double s2 = 0.0, x2 = 0.0;
+    for (int b = threadIdx.x; b < P.NB; b += blockDim.x) { s2 += P.block_part[4 * (size_t)b]; x2 += P.block_part[4 * (size_t)b + 1]; }
+    double cs2 = 0.0, cx2 = 0.0;
+    for (int c = threadIdx.x; c < P.Nc; c += blockDim.x) {
+        if (P.cam_fixed[c]) continue;
+#pragma unroll
+        for (int a = 0; a < 6; a++) cs2 += dc[6 * (size_t)c + a] * dc[6 * (size_t)c + a];
+#pragma unroll
+        for (int a = 0; a < 3; a++) cx2 += P.cam_r[3 * (size_t)c + a] * P.cam_r[3 * (size_t)c + a] + P.cam_t[3 * (size_t)c + a] * P.cam_t[3 * (size_t)c + a];
+    }
+    acc = block_sum(acc, sh); mp = block_sum(mp, sh); mc = block_sum(mc, sh);
+    s2 = block_sum(s2, sh); x2 = block_sum(x2, sh); cs2 = block_sum(cs2, sh); cx2 = block_sum(cx2, sh);
+    if (threadIdx.x == 0) {
+        P.scalars[SC_MODEL] = -(acc + mp);
+        P.scalars[SC_MODEL_PRIOR_CAM] = -mc;
+        P.scalars[SC_STEP2] = s2; P.scalars[SC_X2] = x2;
+        P.scalars[SC_STEP2_CAM] = cs2; P.scalars[SC_X2_CAM] = cx2;
+    }
+}
+void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st) {
+    if (P.Nt) k_model_tiles<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P, dc);
+    if (P.NB) k_point_stats<<<P.NB, 256, 0, st>>>(P);
+    k_model_reduce<<<1, RED_BLOCK, 0, st>>>(P, dc);
+}
+
+// max-norm of the gradient over free blocks: SC_GMAX (points, local), SC_GMAX_CAM (replicated)
+__global__ void __launch_bounds__(RED_BLOCK) k_grad_max(DevProblem P) {
+    __shared__ double sh[33];
+    double gm = 0.0, gcm = 0.0;
+    for (int b = threadIdx.x; b < P.NB; b += blockDim.x) gm = fmax(gm, P.block_part[4 * (size_t)b + 2]);
+    for (int i = threadIdx.x; i < 6 * P.Nc; i += blockDim.x)
+        if (!P.cam_fixed[i / 6]) gcm = fmax(gcm, fabs(P.gc[i]));
+    gm = block_max(gm, sh); gcm = block_max(gcm, sh);
+    if (threadIdx.x == 0) { P.scalars[SC_GMAX] = gm; P.scalars[SC_GMAX_CAM] = gcm; }
+}
+void launch_grad_max(const DevProblem& P, cudaStream_t st) {
+    if (P.NB) k_point_stats<<<P.NB, 256, 0, st>>>(P);
+    k_grad_max<<<1, RED_BLOCK, 0, st>>>(P);
+}
+
+}  // namespace sba

@@ -1,0 +1,185 @@
+// sba_kernels_schur.cu -- K2: normal-equation blocks, point-block inversion,
+// SCHUR_JACOBI preconditioner, and the implicit Schur operator S x.
+//
+// What ceres::Solve does for the reference behind modularsbasolver.cpp:938
+// (SchurEliminator / ImplicitSchurComplement / SchurJacobiPreconditioner); the
+// in-tree statement of the same algebra is g2o's BlockSolver::solve
+// (modules/g2o/g2o/core/block_solver.hpp:329-479).
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+// ---------------------------------------------------------------------------
+// priors: FixedSizeNormalPrior<3,3>  r = A (x - b), J = A
+// (costfunctors/fixedsizenormalprior.h:89-108).  One thread per target group.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ const double* prior_target(const DevProblem& P, int kind, int idx) {
+    return kind == 0 ? P.pts + 4 * (size_t)idx : (kind == 1 ? P.cam_r + 3 * (size_t)idx : P.cam_t + 3 * (size_t)idx);
+}
+
+// prior residuals; a single block so the cost sum is a fixed tree
+__global__ void __launch_bounds__(RED_BLOCK) k_prior_eval(DevProblem P) {
+    __shared__ double sh[33];
+    double acc = 0.0, acc_cam = 0.0;   // point priors / camera priors (the latter are replicated on every rank)
+    for (int g = threadIdx.x; g < P.Ngroup; g += blockDim.x) {
+        const int is_cam = P.pg_kind[g] != 0;
+        const double* x = prior_target(P, P.pg_kind[g], P.pg_index[g]);
+        for (int i = P.pg_off[g]; i < P.pg_off[g + 1]; i++) {
+            const double* A = P.prior_A + 9 * (size_t)i;
+            const double* b = P.prior_b + 3 * (size_t)i;
+            const double e0 = x[0] - b[0], e1 = x[1] - b[1], e2 = x[2] - b[2];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const double r = A[3 * k] * e0 + A[3 * k + 1] * e1 + A[3 * k + 2] * e2;
+                P.prior_res[3 * (size_t)i + k] = r;
+                if (is_cam) acc_cam += r * r; else acc += r * r;
+            }
+        }
+    }
+    acc = block_sum(acc, sh);
+    acc_cam = block_sum(acc_cam, sh);
+    if (threadIdx.x == 0) { P.scalars[SC_COST_PRIOR] = acc; P.scalars[SC_COST_PRIOR_CAM] = acc_cam; }
+}
+void launch_prior_eval(const DevProblem& P, cudaStream_t st) { k_prior_eval<<<1, RED_BLOCK, 0, st>>>(P); }
+
+// sum of the per-tile observation costs (fixed tree) -> SC_COST_OBS (sum r^2, not halved)
+__global__ void __launch_bounds__(RED_BLOCK) k_cost_reduce(DevProblem P) {
+    __shared__ double sh[33];
+    double acc = 0.0;
+    for (int t = threadIdx.x; t < P.Nt; t += blockDim.x) acc += P.tile_cost[t];
+    acc = block_sum(acc, sh);
+    if (threadIdx.x == 0) P.scalars[SC_COST_OBS] = acc;
+}
+void launch_cost_reduce(const DevProblem& P, cudaStream_t st) { k_cost_reduce<<<1, RED_BLOCK, 0, st>>>(P); }
+
+// adds A^T A and A^T r of the priors to the diagonal blocks (after the observation sums)
+__global__ void k_prior_blocks(DevProblem P, int cameras) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P.Ngroup) return;
+    const int kind = P.pg_kind[g], idx = P.pg_index[g];
+    if ((kind != 0) != (cameras != 0)) return;
+    if (kind == 0 ? P.pt_fixed[idx] : P.cam_fixed[idx]) return;
+    double H[6] = {0, 0, 0, 0, 0, 0}, gg[3] = {0, 0, 0};
+    for (int i = P.pg_off[g]; i < P.pg_off[g + 1]; i++) {
+        const double* A = P.prior_A + 9 * (size_t)i;
+        const double* r = P.prior_res + 3 * (size_t)i;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const double a0 = A[3 * k], a1 = A[3 * k + 1], a2 = A[3 * k + 2];
+            gg[0] += a0 * r[k]; gg[1] += a1 * r[k]; gg[2] += a2 * r[k];
+            H[0] += a0 * a0; H[1] += a0 * a1; H[2] += a0 * a2; H[3] += a1 * a1; H[4] += a1 * a2; H[5] += a2 * a2;
+        }
+    }
+    if (kind == 0) {
+        double* Hp = P.Hpp + 8 * (size_t)idx;
+        double* gp = P.gp + 4 * (size_t)idx;
+#pragma unroll
+        for (int i = 0; i < 6; i++) Hp[i] += H[i];
+        gp[0] += gg[0]; gp[1] += gg[1]; gp[2] += gg[2];
+    } else {
+        const int off = kind == 1 ? 0 : 3;
+        double* Hc = P.Hcc + 21 * (size_t)idx;
+        double* gc = P.gc + 6 * (size_t)idx + off;
+        Hc[sym6(off, off)] += H[0]; Hc[sym6(off, off + 1)] += H[1]; Hc[sym6(off, off + 2)] += H[2];
+        Hc[sym6(off + 1, off + 1)] += H[3]; Hc[sym6(off + 1, off + 2)] += H[4]; Hc[sym6(off + 2, off + 2)] += H[5];
+        gc[0] += gg[0]; gc[1] += gg[1]; gc[2] += gg[2];
+    }
+}
+void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st) {
+    if (P.Ngroup == 0) return;
+    k_prior_blocks<<<cdiv(P.Ngroup, 128), 128, 0, st>>>(P, cameras);
+}
+
+// ---------------------------------------------------------------------------
+// K2a point blocks: thread per point over its point-order records.
+// Hpp = sum A^T A (packed sym), gp = sum A^T res.  Reads 3 of the 4 sectors of
+// each record (A: bytes 0-47, res: bytes 96-111); writes 64 + 32 B per point.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_point_blocks(DevProblem P) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P.Np) return;
+    double H[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+    if (!P.pt_fixed[p]) {
+        const int k0 = __ldg(P.pt_off + p), k1 = __ldg(P.pt_off + p + 1);
+        for (int k = k0; k < k1; k++) {
+            const double* rec = P.prec + (size_t)PREC * k;
+            const double2 a01 = ldg2(rec), a23 = ldg2(rec + 2), a45 = ldg2(rec + 4), r = ldg2(rec + 12);
+            const double A0 = a01.x, A1 = a01.y, A2 = a23.x, A3 = a23.y, A4 = a45.x, A5 = a45.y;
+            H[0] += A0 * A0 + A3 * A3; H[1] += A0 * A1 + A3 * A4; H[2] += A0 * A2 + A3 * A5;
+            H[3] += A1 * A1 + A4 * A4; H[4] += A1 * A2 + A4 * A5; H[5] += A2 * A2 + A5 * A5;
+            g[0] += A0 * r.x + A3 * r.y; g[1] += A1 * r.x + A4 * r.y; g[2] += A2 * r.x + A5 * r.y;
+        }
+    }
+    double* Hp = P.Hpp + 8 * (size_t)p;
+    st2(Hp, H[0], H[1]); st2(Hp + 2, H[2], H[3]); st2(Hp + 4, H[4], H[5]); st2(Hp + 6, 0.0, 0.0);
+    double* gp = P.gp + 4 * (size_t)p;
+    st2(gp, g[0], g[1]); st2(gp + 2, g[2], 0.0);
+}
+void launch_point_blocks(const DevProblem& P, cudaStream_t st) {
+    if (P.Np == 0) return;
+    k_point_blocks<<<cdiv(P.Np, 256), 256, 0, st>>>(P);
+}
+
+// ---------------------------------------------------------------------------
+// K2b camera blocks: warp per tile.  Every lane accumulates its slots'
+// Jc^T Jc (21 unique) and Jc^T res (6) with Jc = [C | -A]; a fixed xor-shuffle
+// tree folds the 32 lanes; lane 0 writes the tile partial.  k_tile_reduce then
+// sums the tiles of each camera in tile order.
+// Reads 112 B/obs (res, C, A planes, coalesced).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProblem P) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
+    if (tile >= P.Nt) return;
+    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    const size_t Ns = (size_t)P.Ns;
+    double H[21], g[6];
+#pragma unroll
+    for (int i = 0; i < 21; i++) H[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) g[i] = 0.0;
+    for (int s = start + lane; s < start + len; s += 32) {
+        double j0[6], j1[6];   // the two rows of Jc
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            j0[a] = __ldg(P.Cc + (size_t)a * Ns + s);
+            j1[a] = __ldg(P.Cc + (size_t)(3 + a) * Ns + s);
+            j0[3 + a] = -__ldg(P.Ac + (size_t)a * Ns + s);
+            j1[3 + a] = -__ldg(P.Ac + (size_t)(3 + a) * Ns + s);
+        }
+        const double r0 = __ldg(P.res + s), r1 = __ldg(P.res + Ns + s);
+        int q = 0;
+#pragma unroll
+        for (int a = 0; a < 6; a++) {
+            g[a] += j0[a] * r0 + j1[a] * r1;
+#pragma unroll
+            for (int b = a; b < 6; b++) H[q++] += j0[a] * j0[b] + j1[a] * j1[b];
+        }
+    }
+    double* out = P.tile_part + (size_t)TP * tile;
+#pragma unroll
+    for (int i = 0; i < 21; i++) { const double v = warp_sum(H[i]); if (lane == 0) out[i] = v; }
+#pragma unroll
+    for (int i = 0; i < 6; i++) { const double v = warp_sum(g[i]); if (lane == 0) out[21 + i] = v; }
+}
+
+// thread per (camera, component): fixed-order sum over the camera's tiles.
+// n components starting at tile-partial offset `src`; dst AoS with stride n.
+__global__ void k_tile_reduce(DevProblem P, int src, int n, double* dst, int zero_fixed) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.Nc * n) return;
+    const int c = i / n, comp = i - c * n;
+    double acc = 0.0;
+    if (!(zero_fixed && P.cam_fixed[c])) {
+        const int t0 = P.cam_tile_off[c], t1 = P.cam_tile_off[c + 1];
+        for (int t = t0; t < t1; t++) acc += P.tile_part[(size_t)TP * t + src + comp];
+    }
+    dst[i] = acc;
+}
+void launch_camera_blocks(const DevProblem& P, cudaStream_t st) {
+    if (P.Nt) k_camera_blocks<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    k_tile_reduce<<<cdiv(P.Nc * 21, 256), 256, 0, st>>>(P, 0, 21, P.Hcc, 1);
+    k_tile_reduce<<<cdiv(P.Nc * 6, 256), 256, 0, st>>>(P, 21, 6, P.gc, 1);
+}
+
+}  // namespace sba
