@@ -99,7 +99,8 @@ enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, F
 void launch_pose_cache(const DevProblem& P, cudaStream_t st);
 void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st);   // K1 / K1c, camera order
 void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p: point-order records
-void launch_prior_eval(const DevProblem& P, cudaStream_t st);                    // prior residuals + their cost
+void launch_prior_eval(const DevProblem& P, int store, cudaStream_t st);         // prior residuals (stored if store) + their cost
+void launch_pack_tail(const DevProblem& P, double* tail, cudaStream_t st);
 void launch_cost_reduce(const DevProblem& P, cudaStream_t st);                   // tile costs -> SC_COST_OBS
 void launch_point_blocks(const DevProblem& P, cudaStream_t st);                  // K2a: Hpp, gp
 void launch_camera_blocks(const DevProblem& P, cudaStream_t st);                 // K2b: tile partials + per-camera reduce -> Hcc, gc

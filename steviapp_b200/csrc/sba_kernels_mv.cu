@@ -105,7 +105,7 @@ __device__ __forceinline__ double finish_terms(const DevProblem& P, int c, int a
         for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * x[6 * (size_t)c + b];
         v += hsign * hx;
     }
-    if (damp) v += P.lam_c[i] * x[i];
+    if (damp == 1 || (damp == 2 && P.cam_fixed[c])) v += P.lam_c[i] * x[i];   // 2: rows of fixed cameras only (test hook)
     if (base) v += base[i];
     return v;
 }

@@ -18,7 +18,7 @@ __device__ __forceinline__ const double* prior_target(const DevProblem& P, int k
 }
 
 // prior residuals; a single block so the cost sum is a fixed tree
-__global__ void __launch_bounds__(RED_BLOCK) k_prior_eval(DevProblem P) {
+__global__ void __launch_bounds__(RED_BLOCK) k_prior_eval(DevProblem P, int store) {
     __shared__ double sh[33];
     double acc = 0.0, acc_cam = 0.0;   // point priors / camera priors (the latter are replicated on every rank)
     for (int g = threadIdx.x; g < P.Ngroup; g += blockDim.x) {
@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(RED_BLOCK) k_prior_eval(DevProblem P) {
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 const double r = A[3 * k] * e0 + A[3 * k + 1] * e1 + A[3 * k + 2] * e2;
-                P.prior_res[3 * (size_t)i + k] = r;
+                if (store) P.prior_res[3 * (size_t)i + k] = r;
                 if (is_cam) acc_cam += r * r; else acc += r * r;
             }
         }
@@ -40,7 +40,14 @@ __global__ void __launch_bounds__(RED_BLOCK) k_prior_eval(DevProblem P) {
     acc_cam = block_sum(acc_cam, sh);
     if (threadIdx.x == 0) { P.scalars[SC_COST_PRIOR] = acc; P.scalars[SC_COST_PRIOR_CAM] = acc_cam; }
 }
-void launch_prior_eval(const DevProblem& P, cudaStream_t st) { k_prior_eval<<<1, RED_BLOCK, 0, st>>>(P); }
+void launch_prior_eval(const DevProblem& P, int store, cudaStream_t st) { k_prior_eval<<<1, RED_BLOCK, 0, st>>>(P, store); }
+
+// multi-GPU: this rank's (sum r^2, cheirality flag) appended to the Hcc|gc all-reduce payload
+__global__ void k_pack_tail(DevProblem P, double* tail) {
+    tail[0] = P.scalars[SC_COST_OBS] + P.scalars[SC_COST_PRIOR];
+    tail[1] = P.flags[FL_CHEIRALITY] ? 1.0 : 0.0;
+}
+void launch_pack_tail(const DevProblem& P, double* tail, cudaStream_t st) { k_pack_tail<<<1, 1, 0, st>>>(P, tail); }
 
 // sum of the per-tile observation costs (fixed tree) -> SC_COST_OBS (sum r^2, not halved)
 __global__ void __launch_bounds__(RED_BLOCK) k_cost_reduce(DevProblem P) {

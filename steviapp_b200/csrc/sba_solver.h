@@ -1,0 +1,130 @@
+// sba_solver.h -- host side of libsba_b200.so: problem ingest, layout building,
+// the Levenberg-Marquardt driver and the NCCL plumbing.  C++ only; the C ABI in
+// include/sba_b200.h is a thin shell over this class.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "sba_b200.h"
+#include "sba_device.h"
+
+namespace sba {
+
+// NCCL loaded lazily with dlopen (the single-GPU path has no NCCL dependency)
+struct Comm {
+    bool active = false;
+    int rank = 0, nranks = 1;
+    void* comm = nullptr;
+    int init(int rank, int nranks, const uint8_t* id128, std::string& err);
+    int allreduce_sum(double* buf, size_t n, cudaStream_t st, std::string& err);
+    int allreduce_max(double* buf, size_t n, cudaStream_t st, std::string& err);
+    void destroy();
+    static int unique_id(uint8_t* id128, std::string& err);
+};
+
+struct DeviceArena {
+    std::vector<void*> ptrs;
+    size_t bytes = 0;
+    template <class T>
+    cudaError_t alloc(T** p, size_t n, bool zero = true) {
+        *p = nullptr;
+        if (n == 0) n = 1;
+        cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+        if (e != cudaSuccess) return e;
+        ptrs.push_back(*p);
+        bytes += n * sizeof(T);
+        if (zero) e = cudaMemset(*p, 0, n * sizeof(T));
+        return e;
+    }
+    void release() {
+        for (void* p : ptrs) cudaFree(p);
+        ptrs.clear();
+        bytes = 0;
+    }
+};
+
+enum Phase { PH_LINEARIZE = 0, PH_SCHUR, PH_PCG, PH_UPDATE, PH_H2D, PH_D2H, PH_N };
+
+struct PhaseTimer {
+    struct Span { cudaEvent_t a, b; int phase; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> pool;
+    size_t used = 0;
+    cudaEvent_t get();
+    void begin(int phase, cudaStream_t st);
+    void end(cudaStream_t st);
+    void collect(double* ms_by_phase);   // synchronises
+    void reset() { spans.clear(); used = 0; }
+    void destroy();
+};
+
+class Solver {
+public:
+    explicit Solver(const sba_options& o);
+    ~Solver();
+    int open_device();
+
+    int set_intrinsics(int32_t n, const double* intr10);
+    int set_poses(double* raxis, double* t, int32_t n, const int32_t* model, const uint8_t* fixed, const uint8_t* kind);
+    int set_points(double* xyz, int32_t n, const uint8_t* fixed);
+    int add_observations(int32_t n, const int32_t* cam, const int32_t* pt, const double* uv, const double* info);
+    int add_priors(int32_t n, const int32_t* kind, const int32_t* index, const double* A9, const double* b3);
+    int finalize();
+    int upload_parameters();
+    int download_parameters();
+    int evaluate(double* cost, double* residuals, double* jac_cam, double* jac_pt);
+    int normal_blocks(double* gc, double* gp, double* Hcc, double* Hpp);
+    int schur_matvec(const double* lam_c, const double* lam_p, const double* x, double* y, double* rhs);
+    int solve(int copy_params, sba_summary* sum);
+    int time_stage(int stage, int reps, double* ms);
+    int triangulate(int32_t n_points, const int32_t* view_off, const int32_t* view_cam, const double* view_uv,
+                    double* xyz_out, uint8_t* ok_out, double* ms_kernel);
+    int comm_init(int rank, int nranks, const uint8_t* id128);
+
+    sba_options opt;
+    std::string err;
+    sba_iteration_callback cb = nullptr;
+    void* cb_user = nullptr;
+    DevProblem P{};
+    bool finalized = false;
+
+private:
+    int fail(int code, const std::string& msg);
+    int cuda_fail(cudaError_t e, const char* what);
+    int read_scalars();                      // device scalars/flags -> h_scalars/h_flags (synchronises)
+    int linearize(double* cost, bool* eval_ok);            // K0,K1,K1p,K2a,K2b (+ all-reduce) at the current point
+    int cost_only(double* cost, bool* eval_ok);            // K0,K1c
+    int build_rhs_and_preconditioner(bool* ok);            // damped inverse, reduced rhs, Minv
+    int schur_apply(const double* x, double* y);           // y = S x  (x zero at fixed cameras)
+    int run_pcg(int* iters);
+
+    // host copies (caller order)
+    double* h_raxis = nullptr; double* h_t = nullptr; double* h_xyz = nullptr;   // caller-owned
+    int32_t Nc = 0, Np = 0, Nm = 0;
+    std::vector<int32_t> cam_model; std::vector<uint8_t> cam_fixed, cam_kind, pt_fixed;
+    std::vector<double> intr;
+    std::vector<int32_t> obs_cam, obs_pt; std::vector<double> obs_uv, obs_info; bool has_info = false, info_missing = false;
+    std::vector<int32_t> prior_kind, prior_index; std::vector<double> prior_A, prior_b;
+    std::vector<int32_t> slot_of_obs;
+    int32_t* d_slot_of_obs = nullptr;
+
+    DeviceArena arena;
+    cudaStream_t st = nullptr;
+    double* h_scalars = nullptr;   // pinned, SC_N
+    int32_t* h_flags = nullptr;    // pinned, FL_N
+    double* d_red = nullptr;       // small device buffer for scalar all-reduces
+    double* h_stage = nullptr;     // pinned staging for parameters
+    size_t h_stage_n = 0;
+    double* d_stage = nullptr; size_t d_stage_n = 0;
+    double* d_HG = nullptr;        // Hcc | gc | tail(2) contiguous
+    Comm comm;
+    PhaseTimer timer;
+    int launches = 0;
+    bool scaling_done = false;
+};
+
+}  // namespace sba
