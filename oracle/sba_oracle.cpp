@@ -632,6 +632,11 @@ int oracle_uv_from_dir(const double* xn, const double* in, double* uv) {
     return 0;
 }
 
+// test hooks on the LibStevi restatements, pinned by the reference's own vectors
+// (tests/test_geometry/testRotations.cpp:25-78, tests/test_functional_utils/main.cpp:198-218)
+void oracle_angle_axis_rotate(const double* r, const double* x, double* out) { angle_axis_rotate<double>(r, x, out); }
+void oracle_rigid_inverse(const double* r, const double* t, double* ri, double* ti) { rigid_inverse<double>(r, t, ri, ti); }
+
 int oracle_evaluate(const oracle_problem* p, int num_threads, double* cost, double* residuals,
                     double* jac_cam, double* jac_pt, uint8_t* failed) {
     const int nt = nthreads(num_threads);

@@ -85,6 +85,10 @@ void oracle_dir_from_uv(const double* uv, const double* intr10, double* dir3);
  * synthetic generators only. xn = normalised undistorted (P.x/P.z, P.y/P.z). */
 int oracle_uv_from_dir(const double* xn2, const double* intr10, double* uv2);
 
+/* R(r) x and RigidBodyTransform::inverse (LibStevi restatements) */
+void oracle_angle_axis_rotate(const double* r, const double* x, double* out);
+void oracle_rigid_inverse(const double* r, const double* t, double* ri, double* ti);
+
 /* residuals (2*n_obs), jac_cam (n_obs*2*6 row-major: [d/dr(3) d/dt(3)]),
  * jac_pt (n_obs*2*3), all in the caller's observation order; any output may be
  * NULL.  cost = 1/2 sum r^2 including priors.  Returns 0, or 1 if a plane
