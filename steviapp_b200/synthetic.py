@@ -86,7 +86,8 @@ def axis_angle_to_rotmat(r):
 
 def make_scene(shape="small", seed=None, n_cams=None, n_pts=None, n_obs=None, noise_px=0.5,
                init_noise=(0.01, 0.05, 0.1), mixed=False, spherical=False, shuffle=None,
-               ring_radius=30.0, cloud_radius=10.0, cloud_height=5.0, window=None, intrinsics=None):
+               ring_radius=30.0, cloud_radius=10.0, cloud_height=5.0, window=None, far_fraction=0.3,
+               intrinsics=None):
     """Returns a dict of numpy arrays describing one BA problem (truth, initial values, observations, priors)."""
     if shape is not None:
         nc, npt, no = SHAPES[shape]
@@ -146,8 +147,18 @@ def make_scene(shape="small", seed=None, n_cams=None, n_pts=None, n_obs=None, no
     order = np.argsort(rng.random((n_pts, window), dtype=np.float32), axis=1).astype(np.int32)
     take = np.arange(window)[None, :] < k[:, None]
     obs_pt = np.repeat(np.arange(n_pts, dtype=np.int32), k)
-    off = order[take]                                      # row-major: point-major order
-    obs_cam = ((i0[obs_pt] + off - window // 2) % n_cams).astype(np.int32)
+    off = order[take].astype(np.int64) - window // 2       # row-major: point-major order
+    # long-range links: a fraction of the views comes from anywhere on the ring (every camera looks at
+    # the centre, so they are geometrically valid).  View j of a point draws from the j-th stratum of
+    # the ring outside its window, so the cameras of one point stay distinct.
+    far_len = n_cams - window - 1
+    strat = far_len // window if window > 0 else 0
+    if far_fraction > 0 and strat >= 1:
+        col = np.broadcast_to(np.arange(window, dtype=np.int64), (n_pts, window))[take]
+        is_far = rng.random(off.size) < far_fraction
+        far_off = (window - window // 2) + col * strat + np.floor(rng.random(off.size) * strat).astype(np.int64)
+        off = np.where(is_far, far_off, off)
+    obs_cam = ((i0[obs_pt] + off) % n_cams).astype(np.int32)
     del order, take
 
     # ---- pixels through the forward model

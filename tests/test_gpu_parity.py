@@ -216,6 +216,7 @@ def test_venice_scale_properties():
     """Full BASELINE size (1778 / 993923 / 5001946): size-independent properties instead of the oracle."""
     sc = synthetic.make_scene("venice")
     s, _ = gpu_solver(sc, pcg_check_every=4)
+    s.finalize()
     assert s.sizes()["n_obs"] == 5001946
     e = s.evaluate(residuals=True, jacobians=False)
     # cost equals half the squared norm of the returned residuals (+ the 4 GCP priors)
