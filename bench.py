@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- LM iterations/s (+ residual/Jacobian Mobs/s, HBM GB/s vs peak) on the synthetic
+Venice-shape bundle adjustment (1778 cameras / 993 923 points / 5 001 946 observations).
+
+  python bench.py --gpus N --steps K --warmup W            B200 engine (libsba_b200.so)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path (oracle port), host cores
+
+A "step" is ONE Levenberg-Marquardt iteration: damping + point-block inversion + reduced rhs +
+SCHUR_JACOBI preconditioner + PCG on the implicit Schur complement + back-substitution + trial cost
+(+ re-linearisation when the step is accepted).  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "lm_iterations_per_s"
+UNIT = "LM iters/s"
+FIXED = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
+SAMPLE_DIV = 16          # CPU legs run on a Venice-shape scene with 1/16 of the points (same cameras, same views/point)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--shape", default="venice")
+    ap.add_argument("--pcg-tol", type=float, default=1e-10)
+    ap.add_argument("--pcg-max-iters", type=int, default=500)
+    ap.add_argument("--pcg-check-every", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.stop = threading.Event()
+        self.th = None
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.15)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- CPU legs (oracle)
+def sample_scene(shape):
+    from steviapp_b200 import synthetic
+    nc, npt, no = synthetic.SHAPES[shape]
+    if shape in ("venice", "city"):
+        return synthetic.make_scene(shape, n_pts=npt // SAMPLE_DIV, n_obs=no // SAMPLE_DIV), no
+    return synthetic.make_scene(shape), no
+
+
+def cpu_leg(shape, steps, warmup, pcg_tol, pcg_max, threads=0):
+    """Times the CPU restatement of the reference (oracle/) on a bounded sample; returns the cpu_baseline dict.
+    value = LM iters/s extrapolated to the full workload: iters/s on the sample x (sample obs / full obs)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    sc, full_obs = sample_scene(shape)
+    nthreads = oracle_py.num_threads() if threads <= 0 else threads
+    kw = dict(num_threads=nthreads, pcg_rel_tol=pcg_tol, pcg_max_iters=pcg_max, **FIXED)
+    if warmup > 0:
+        oracle_py.Problem(sc).solve(max_iterations=min(warmup, 1), **kw)
+    p = oracle_py.Problem(sc)
+    t0 = time.perf_counter()
+    s = p.solve(max_iterations=steps, **kw)
+    dt = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    oracle_py.Problem(sc).evaluate(threads=nthreads)
+    t_eval = time.perf_counter() - t1
+    it_s_sample = s["iterations"] / dt
+    scale = sc["n_obs"] / full_obs
+    return {
+        "value": it_s_sample * scale, "unit": UNIT, "cores": nthreads, "kind": "port",
+        "sample": (f"{shape}-shape scene at 1/{SAMPLE_DIV} of the points: {sc['n_cams']} cameras / {sc['n_pts']} points / "
+                   f"{sc['n_obs']} observations, {s['iterations']} LM iterations in {dt:.2f} s "
+                   f"({s['pcg_iterations_total']} PCG iterations); value = sample iters/s x {scale:.5f} (observation ratio)"),
+        "sample_iters_per_s": it_s_sample, "sample_seconds": dt, "pcg_iterations": s["pcg_iterations_total"],
+        "final_cost": s["final_cost"], "residual_jacobian_mobs_per_s": sc["n_obs"] / t_eval / 1e6,
+        "note": "CPU restatement of the reference (not Ceres): the reference itself needs Eigen/Ceres/Qt/LibStevi, absent here",
+    }
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_leg(a.shape, max(a.steps, 1), a.warmup, a.pcg_tol, a.pcg_max_iters)
+    v = cb["value"]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 / v if v else None, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": bench_config(a), "cpu_baseline": cb,
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def bench_config(a):
+    from steviapp_b200 import synthetic
+    nc, npt, no = synthetic.SHAPES[a.shape]
+    return {"workload": f"synthetic {a.shape}-shape BA: {nc} cameras / {npt} points / {no} observations, plane cost, "
+                        "intrinsics constant, first camera fixed, 4 GCP priors",
+            "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
+            "linear_solver": "implicit Schur complement + SCHUR_JACOBI PCG",
+            "step": "one LM iteration, fixed count (tolerances 0), every run restarts from the same initial values",
+            "l2": "working set ~1.2 GB per evaluation >> 126 MB L2 (no flush needed)",
+            "parallelism": f"points sharded over {a.gpus} GPU(s), cameras replicated"}
+
+
+# --------------------------------------------------------------------------- B200 arm
+# algorithmic bytes per observation of the kernels bench.py reports on (DESIGN.md "Kernels")
+ALG_BYTES = {
+    "k_residual_jacobian": 136,      # in 16 uv + 4 idx (+ point gather from L2), out 16 res + 48 C + 48 A   (J_t = -J_X form)
+    "k_camera_pass": 132,            # 48 C + 48 A + 4 idx + 32 gathered y_p
+    "k_point_pass": 100,             # 96 record + 4 cam idx (+ 8 B/obs of y_p / Hinv per point, not counted)
+}
+STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6}
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from steviapp_b200 import SBASolver, synthetic, comm_unique_id
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl b200 needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    t0 = time.perf_counter()
+    scene = synthetic.make_scene(a.shape)
+    full_obs = scene["n_obs"]
+    if world > 1:
+        scene = synthetic.shard_scene(scene, rank, world)
+    t_gen = time.perf_counter() - t0
+
+    s = SBASolver(device=local, pcg_rel_tol=a.pcg_tol, pcg_max_iters=a.pcg_max_iters,
+                  pcg_check_every=a.pcg_check_every, **FIXED)
+    if world > 1:
+        uid = [comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        s.comm_init(rank, world, uid[0])
+    t0 = time.perf_counter()
+    raxis, t, pts = synthetic.load_into(s, scene)
+    s.finalize()
+    t_ingest = time.perf_counter() - t0
+    init = (raxis.copy(), t.copy(), pts.copy())
+
+    def reset():
+        raxis[:] = init[0]; t[:] = init[1]; pts[:] = init[2]
+        s.upload_parameters()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxr(x):
+        if world == 1:
+            return x
+        v = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        return float(v.item())
+
+    # ---- warm-up (untimed): W LM iterations, resident
+    reset()
+    if a.warmup > 0:
+        s.solve(max_iterations=a.warmup, copy_params=False)
+
+    # ---- `value`: K LM iterations, inputs resident in HBM, device time (CUDA events on the solver's stream)
+    reset()
+    barrier()
+    with ClockSampler(local) as clk:
+        w0 = time.perf_counter()
+        r = s.solve(max_iterations=a.steps, copy_params=False)
+        barrier()
+        wall = time.perf_counter() - w0
+    assert r["iterations"] == a.steps, r
+    ms_total = maxr(r["ms_total"])
+    wall = maxr(wall)
+    value = a.steps / (ms_total * 1e-3)
+    final_cost = r["final_cost"]
+
+    # ---- `e2e`: the same K LM iterations through the public call with HOST buffers: every step uploads the
+    # parameter blocks (pinned staging), runs one LM iteration and reads the updated blocks back.
+    raxis[:] = init[0]; t[:] = init[1]; pts[:] = init[2]
+    barrier()
+    w0 = time.perf_counter()
+    e2e_launches = 0
+    for _ in range(a.steps):
+        rr = s.solve(max_iterations=1, copy_params=True)
+        e2e_launches += rr["kernel_launches"]
+    barrier()
+    e2e_wall = maxr(time.perf_counter() - w0)
+    nbytes = 8 * (raxis.size + t.size + pts.size)
+    e2e = {"value": a.steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
+           "protocol": "K calls of sba_solve(max_iterations=1, copy_params=1); host wall clock between device synchronisations"}
+
+    # ---- kernel-level numbers (rank 0's shard): CUDA events inside the library around back-to-back launches
+    reset()
+    n_obs_local = s.sizes()["n_obs"]
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    kern = {}
+    for name, stage in STAGE.items():
+        ms = s.time_stage(stage, 20)
+        kern[name] = {"ms": ms, "GBps": ALG_BYTES[name] * n_obs_local / (ms * 1e-3) / 1e9, "Mobs_per_s": n_obs_local / ms / 1e3}
+    pcg_per_step = r["pcg_iterations_total"] / max(r["iterations"], 1)
+    share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
+    dom = max(share, key=share.get)
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
+                "frac": kern[dom]["GBps"] / peak, "traffic": traffic, "peak_source": peak_kind,
+                "alg_bytes_per_obs": ALG_BYTES[dom], "obs_per_launch": n_obs_local,
+                "share_of_step": share[dom] / (ms_total / a.steps),
+                "kernels": {k: {"ms": v["ms"], "GBps": v["GBps"], "frac": v["GBps"] / peak, "alg_bytes_per_obs": ALG_BYTES[k]}
+                            for k, v in kern.items()}}
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cpu = cpu_leg(a.shape, 2, 1, a.pcg_tol, a.pcg_max_iters)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_total / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": bench_config(a),
+            "clocks": clk.summary(), "e2e": e2e, "gpu_launches": r["kernel_launches"],
+            "roofline": roofline, "cpu_baseline": cpu,
+            "residual_jacobian_mobs_per_s": kern["k_residual_jacobian"]["Mobs_per_s"] * (full_obs / n_obs_local if world > 1 else 1.0),
+            "pcg_iterations_per_step": pcg_per_step, "final_cost": final_cost, "initial_cost": r["initial_cost"],
+            "phase_ms": {k: r[k] for k in ("ms_linearize", "ms_schur", "ms_pcg", "ms_update")},
+            "wall_ms_per_step": wall * 1e3 / a.steps, "ingest_s": t_ingest, "scene_gen_s": t_gen,
+        }
+        print(json.dumps(line), flush=True)
+    s.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
