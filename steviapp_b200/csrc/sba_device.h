@@ -10,18 +10,18 @@ namespace sba {
 constexpr int TILE_SLOTS = 256;      // max observation slots per warp tile (multiple of 32)
 constexpr int WARPS_PER_BLOCK = 8;   // tile kernels: 256 threads
 constexpr int RED_BLOCK = 1024;      // single-block deterministic reductions
-constexpr int PREC = 16;             // doubles per point-order record (128 B = one L2 line)
+constexpr int HP = 12;               // doubles per heavy-window partial
 constexpr int TP = 28;               // doubles per tile partial
 
 // All arrays are device pointers.  "slot" = position in the camera-sorted,
 // 32-aligned observation order (padding slots have obs_pt = -1 and all-zero J).
-// "pos" = position in the point-sorted order (by-point CSR, no padding).
+// "q slot" = position in the point-sorted, window-packed order.
 //
 // The Jacobian is stored compressed: for every observation
 //   A = d res / d X (2x3)  and  C = d res / d rAxis (2x3);   d res / d t = -A exactly,
 // so Jc = [C | -A], Jp = A.  It is kept twice, once per traversal order:
 //   camera order : SoA planes res[2], C[6], A[6] over slots   (coalesced warp-per-tile passes)
-//   point order  : 128-byte records {A[6], C[6], res[2], pad[2]} over pos (thread-per-point passes)
+//   point order  : SoA planes qres[2], qC[6], qA[6] over q slots (thread-per-slot passes, segmented warp reductions)
 struct DevProblem {
     int32_t Nc, Np, No, Ns, Nt, Nm, Nprior;
     // cameras (replicated on every rank)
@@ -44,17 +44,28 @@ struct DevProblem {
     int32_t* tile_start;  // Nt
     int32_t* tile_len;    // Nt
     int32_t* cam_tile_off;// Nc+1 (tiles of camera c are cam_tile_off[c]..cam_tile_off[c+1])
-    // by-point CSR over pos
-    int32_t* pt_off;      // Np+1
-    int32_t* pos_slot;    // No: slot of the observation at pos
-    int32_t* pos_cam;     // No: camera of the observation at pos
-    double* pos_uv;       // 2*No: (u,v) in point order (static copy)
-    double* pos_info;     // 4*No AoS or nullptr
+    // point order ("q slots"): observations grouped by point; a point with k <= 32 observations never
+    // straddles a 32-slot window (padding slots have q_pt = -1), a point with k > 32 ("heavy") owns whole
+    // windows.  One thread per q slot, warp-shuffle segmented reductions per point.
+    int32_t Nq;           // padded q-slot count (multiple of 32)
+    int32_t Nh;           // heavy points
+    int32_t* pt_off;      // Np+1: CSR offsets in unpadded point order (k = pt_off[p+1]-pt_off[p])
+    int32_t* pt_q0;       // Np: first q slot of the point
+    int32_t* pt_heavy;    // Np: -1, or index into the heavy arrays
+    int32_t* heavy_pt;    // Nh
+    int32_t* heavy_w0;    // Nh+1: first entry of the point's windows in heavy_part
+    double* heavy_part;   // 12 doubles per heavy window
+    int32_t* q_pt;        // Nq, -1 = padding
+    int32_t* q_cam;       // Nq
+    double* q_uv;         // 2*Nq interleaved (static copy)
+    double* q_info;       // 4*Nq AoS or nullptr
     // materialised linearisation
-    double* res;          // 2 planes of Ns
-    double* Cc;           // 6 planes of Ns   (d res / d rAxis)
-    double* Ac;           // 6 planes of Ns   (d res / d X)
-    double* prec;         // PREC*No point-order records
+    double* res;          // 2 planes of Ns   } camera order
+    double* Cc;           // 6 planes of Ns   }   (d res / d rAxis)
+    double* Ac;           // 6 planes of Ns   }   (d res / d X)
+    double* qres;         // 2 planes of Nq   } point order
+    double* qC;           // 6 planes of Nq   }
+    double* qA;           // 6 planes of Nq   }
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -84,6 +95,7 @@ struct DevProblem {
     double* cam_saved;    // 6*Nc
     double* xz;           // 6*Nc: input vector with fixed cameras zeroed
     double* pcg_x, *pcg_r, *pcg_z, *pcg_p, *pcg_q, *rhs;   // 6*Nc each
+    double* pcg_part;     // 2 * pcg_blocks per-block partials of p.q and r.z
     double* block_part;   // 4*NB per-block partial sums for scalar reductions over points
     int32_t NB;           // number of point blocks (ceil(Np/256))
     double* scalars;      // SC_N doubles
@@ -92,13 +104,13 @@ struct DevProblem {
 
 enum { SC_COST = 0, SC_RZ = 1, SC_RZ0 = 2, SC_PQ = 3, SC_MODEL = 4, SC_STEP2 = 5, SC_X2 = 6, SC_GMAX = 7,
        SC_COST_OBS = 8, SC_COST_PRIOR = 9, SC_MODEL_PRIOR = 10, SC_COST_PRIOR_CAM = 11, SC_MODEL_PRIOR_CAM = 12,
-       SC_STEP2_CAM = 13, SC_X2_CAM = 14, SC_GMAX_CAM = 15, SC_N = 32 };
-enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, FL_N = 8 };
+       SC_STEP2_CAM = 13, SC_X2_CAM = 14, SC_GMAX_CAM = 15, SC_RZ_NEXT = 16, SC_N = 32 };
+enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, FL_PCG_ITERS_NEXT = 4, FL_N = 8 };
 
 // ---- launch wrappers (sba_kernels.cu); all asynchronous on `st` ----
 void launch_pose_cache(const DevProblem& P, cudaStream_t st);
 void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st);   // K1 / K1c, camera order
-void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p: point-order records
+void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p: point-order planes
 void launch_prior_eval(const DevProblem& P, int store, cudaStream_t st);         // prior residuals (stored if store) + their cost
 void launch_pack_tail(const DevProblem& P, double* tail, cudaStream_t st);
 void launch_cost_reduce(const DevProblem& P, cudaStream_t st);                   // tile costs -> SC_COST_OBS
@@ -122,7 +134,10 @@ void launch_camera_finish(const DevProblem& P, const double* x, const double* ba
 void launch_zero_fixed(const DevProblem& P, const double* x, double* xz, cudaStream_t st);   // xz = x, 0 at fixed cameras
 void launch_negate(double* x, int n, cudaStream_t st);
 void launch_pcg_init(const DevProblem& P, cudaStream_t st);       // x=0, r=rhs, z=Minv r, p=z, rz, rz0
-void launch_pcg_update(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z, rz, beta, p (frozen once converged)
+int pcg_blocks(const DevProblem& P);
+void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st);    // q (from tile partials or all-reduced) + p.q partials
+void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z | beta, p (frozen once converged)
+void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st);   // operator pass 2, tile partials only
 void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st);   // SC_MODEL, SC_STEP2, SC_X2 (local part)
 void launch_apply_step(const DevProblem& P, const double* dc, cudaStream_t st);     // save + x += delta
 void launch_restore(const DevProblem& P, cudaStream_t st);

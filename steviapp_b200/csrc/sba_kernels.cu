@@ -40,7 +40,7 @@ void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
 // (J_t = -J_X not stored; 184 B/obs with it).
 // ---------------------------------------------------------------------------
 template <bool JAC>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_residual_jacobian(DevProblem P) {
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(DevProblem P) {
     __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
@@ -108,59 +108,6 @@ void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st) {
     const int nb = cdiv(P.Nt, WARPS_PER_BLOCK);
     if (jac) k_residual_jacobian<true><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
     else k_residual_jacobian<false><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
-}
-
-// ---------------------------------------------------------------------------
-// K1p linearisation in point order: thread per point walks its CSR row, rebuilds
-// the same A, C, res (bitwise the same expressions as K1) and writes one 128-byte
-// record per observation.  In: 16 (uv) + 4 (cam) per obs, 32 per point; out 112
-// useful bytes per obs (128 allocated).
-// ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_linearize_points(DevProblem P) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P.Np) return;
-    const double2 x01 = ldg2(P.pts + 4 * (size_t)p), x23 = ldg2(P.pts + 4 * (size_t)p + 2);
-    const double X[3] = {x01.x, x01.y, x23.x};
-    const int k0 = __ldg(P.pt_off + p), k1 = __ldg(P.pt_off + p + 1);
-    for (int k = k0; k < k1; k++) {
-        const int cam = __ldg(P.pos_cam + k);
-        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
-        double ccr[21];
-#pragma unroll
-        for (int i = 0; i < 10; i++) { const double2 v = ldg2(cc + 2 * i); ccr[2 * i] = v.x; ccr[2 * i + 1] = v.y; }
-        ccr[20] = __ldg(cc + 20);
-        const double* in = P.intr + 10 * __ldg(P.cam_model + cam);
-        double intr[10];
-#pragma unroll
-        for (int i = 0; i < 5; i++) { const double2 v = ldg2(in + 2 * i); intr[2 * i] = v.x; intr[2 * i + 1] = v.y; }
-        const double2 uv = ldg2(P.pos_uv + 2 * (size_t)k);
-        double d[3];
-        dir_from_uv(uv.x, uv.y, intr, d);
-        double W[4];
-        const double* Wp = nullptr;
-        if (P.pos_info) {
-            const double2 w01 = ldg2(P.pos_info + 4 * (size_t)k), w23 = ldg2(P.pos_info + 4 * (size_t)k + 2);
-            W[0] = w01.x; W[1] = w01.y; W[2] = w23.x; W[3] = w23.y;
-            Wp = W;
-        }
-        double r[2] = {0.0, 0.0}, Jc[12], Jp[6];
-        const bool ok = obs_eval<true>(ccr, X, d, Wp, P.cam_kind[cam], r, Jc, Jp);
-        if (!ok) {
-            r[0] = r[1] = 0.0;
-#pragma unroll
-            for (int i = 0; i < 12; i++) Jc[i] = 0.0;
-#pragma unroll
-            for (int i = 0; i < 6; i++) Jp[i] = 0.0;
-        }
-        double* rec = P.prec + (size_t)PREC * k;
-        st2(rec + 0, Jp[0], Jp[1]); st2(rec + 2, Jp[2], Jp[3]); st2(rec + 4, Jp[4], Jp[5]);
-        st2(rec + 6, Jc[0], Jc[1]); st2(rec + 8, Jc[2], Jc[6]); st2(rec + 10, Jc[7], Jc[8]);
-        st2(rec + 12, r[0], r[1]);
-    }
-}
-void launch_linearize_points(const DevProblem& P, cudaStream_t st) {
-    if (P.Np == 0) return;
-    k_linearize_points<<<cdiv(P.Np, 256), 256, 0, st>>>(P);
 }
 
 }  // namespace sba

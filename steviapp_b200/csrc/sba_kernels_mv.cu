@@ -1,60 +1,8 @@
-// sba_kernels_mv.cu -- the two passes of the implicit Schur operator and the
-// back-substitution (K2c / K4 of SURVEY Appendix C).
+// sba_kernels_mv.cu -- pass 2 (camera order) of the implicit Schur operator; pass 1 and the
+// back-substitution live in sba_kernels_points.cu.
 #include "sba_kernel_util.cuh"
 
 namespace sba {
-
-// ---------------------------------------------------------------------------
-// point pass: thread per point over its 128-byte records (A: bytes 0-47,
-// C: bytes 48-95 -> 3 sectors per observation), camera vector gathered (48 B,
-// L1/L2 resident).  x must be zero at fixed cameras.
-//   mode 0: y_p = Hinv * sum_o A^T (C x_r - A x_t)
-//   mode 1: y_p = Hinv * gp
-//   mode 2: dp  = -Hinv * (gp + sum_o A^T (C x_r - A x_t))     (back-substitution,
-//           block_solver.hpp:455-477 analogue)
-// ---------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(256) k_point_pass(DevProblem P, const double* __restrict__ x) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P.Np) return;
-    double u0 = 0.0, u1 = 0.0, u2 = 0.0;
-    if (MODE != 0) {
-        const double* g = P.gp + 4 * (size_t)p;
-        const double2 g01 = ldg2(g), g23 = ldg2(g + 2);
-        u0 = g01.x; u1 = g01.y; u2 = g23.x;
-    }
-    if (MODE != 1) {
-        const int k0 = __ldg(P.pt_off + p), k1 = __ldg(P.pt_off + p + 1);
-        for (int k = k0; k < k1; k++) {
-            const double* rec = P.prec + (size_t)PREC * k;
-            const double* xc = x + 6 * (size_t)__ldg(P.pos_cam + k);
-            const double2 a01 = ldg2(rec), a23 = ldg2(rec + 2), a45 = ldg2(rec + 4);
-            const double2 c01 = ldg2(rec + 6), c23 = ldg2(rec + 8), c45 = ldg2(rec + 10);
-            const double2 x01 = ldg2(xc), x23 = ldg2(xc + 2), x45 = ldg2(xc + 4);
-            // rows of Jc x = C x_r - A x_t
-            const double m0 = c01.x * x01.x + c01.y * x01.y + c23.x * x23.x - (a01.x * x23.y + a01.y * x45.x + a23.x * x45.y);
-            const double m1 = c23.y * x01.x + c45.x * x01.y + c45.y * x23.x - (a23.y * x23.y + a45.x * x45.x + a45.y * x45.y);
-            u0 += a01.x * m0 + a23.y * m1;
-            u1 += a01.y * m0 + a45.x * m1;
-            u2 += a23.x * m0 + a45.y * m1;
-        }
-    }
-    const double* Hp = P.Hinv + 8 * (size_t)p;
-    const double2 h01 = ldg2(Hp), h23 = ldg2(Hp + 2), h45 = ldg2(Hp + 4);
-    double y0 = h01.x * u0 + h01.y * u1 + h23.x * u2;
-    double y1 = h01.y * u0 + h23.y * u1 + h45.x * u2;
-    double y2 = h23.x * u0 + h45.x * u1 + h45.y * u2;
-    double* o = (MODE == 2 ? P.dp : P.y_p) + 4 * (size_t)p;
-    if (MODE == 2) { y0 = -y0; y1 = -y1; y2 = -y2; }
-    st2(o, y0, y1); st2(o + 2, y2, 0.0);
-}
-void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st) {
-    if (P.Np == 0) return;
-    const int nb = cdiv(P.Np, 256);
-    if (mode == 0) k_point_pass<0><<<nb, 256, 0, st>>>(P, x);
-    else if (mode == 1) k_point_pass<1><<<nb, 256, 0, st>>>(P, x);
-    else k_point_pass<2><<<nb, 256, 0, st>>>(P, x);
-}
 
 // ---------------------------------------------------------------------------
 // camera pass: warp per tile, sum_o Jc^T (A y_p) with Jc = [C | -A]; reads the
@@ -133,6 +81,9 @@ void launch_camera_pass(const DevProblem& P, const double* x, const double* base
                         double* out, cudaStream_t st) {
     if (P.Nt) k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
     k_camera_reduce<<<cdiv(P.Nc * 6, 256), 256, 0, st>>>(P, x, base, hsign, damp, finish, out);
+}
+void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st) {
+    if (P.Nt) k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
 }
 void launch_camera_finish(const DevProblem& P, const double* x, const double* base, double hsign, int damp, double* out,
                           cudaStream_t st) {

@@ -98,36 +98,6 @@ void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------
-// K2a point blocks: thread per point over its point-order records.
-// Hpp = sum A^T A (packed sym), gp = sum A^T res.  Reads 3 of the 4 sectors of
-// each record (A: bytes 0-47, res: bytes 96-111); writes 64 + 32 B per point.
-// ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_point_blocks(DevProblem P) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P.Np) return;
-    double H[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
-    if (!P.pt_fixed[p]) {
-        const int k0 = __ldg(P.pt_off + p), k1 = __ldg(P.pt_off + p + 1);
-        for (int k = k0; k < k1; k++) {
-            const double* rec = P.prec + (size_t)PREC * k;
-            const double2 a01 = ldg2(rec), a23 = ldg2(rec + 2), a45 = ldg2(rec + 4), r = ldg2(rec + 12);
-            const double A0 = a01.x, A1 = a01.y, A2 = a23.x, A3 = a23.y, A4 = a45.x, A5 = a45.y;
-            H[0] += A0 * A0 + A3 * A3; H[1] += A0 * A1 + A3 * A4; H[2] += A0 * A2 + A3 * A5;
-            H[3] += A1 * A1 + A4 * A4; H[4] += A1 * A2 + A4 * A5; H[5] += A2 * A2 + A5 * A5;
-            g[0] += A0 * r.x + A3 * r.y; g[1] += A1 * r.x + A4 * r.y; g[2] += A2 * r.x + A5 * r.y;
-        }
-    }
-    double* Hp = P.Hpp + 8 * (size_t)p;
-    st2(Hp, H[0], H[1]); st2(Hp + 2, H[2], H[3]); st2(Hp + 4, H[4], H[5]); st2(Hp + 6, 0.0, 0.0);
-    double* gp = P.gp + 4 * (size_t)p;
-    st2(gp, g[0], g[1]); st2(gp + 2, g[2], 0.0);
-}
-void launch_point_blocks(const DevProblem& P, cudaStream_t st) {
-    if (P.Np == 0) return;
-    k_point_blocks<<<cdiv(P.Np, 256), 256, 0, st>>>(P);
-}
-
-// ---------------------------------------------------------------------------
 // K2b camera blocks: warp per tile.  Every lane accumulates its slots'
 // Jc^T Jc (21 unique) and Jc^T res (6) with Jc = [C | -A]; a fixed xor-shuffle
 // tree folds the 32 lanes; lane 0 writes the tile partial.  k_tile_reduce then
