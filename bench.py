@@ -159,7 +159,7 @@ def bench_config(a):
 # algorithmic bytes per observation of the kernels bench.py reports on (DESIGN.md "Kernels")
 ALG_BYTES = {
     "k_residual_jacobian": 136,      # in 16 uv + 4 idx (+ point gather from L2), out 16 res + 48 C + 48 A   (J_t = -J_X form)
-    "k_camera_pass": 132,            # 48 C + 48 A + 4 idx + 32 gathered y_p
+    "k_camera_pass": 60,             # factored form: 24 Pbar + 4 pt idx + 32 gathered y_p  (materialised form: 132)
     "k_point_pass": 104,             # 48 C + 48 A planes + 4 pt idx + 4 cam idx (camera vector from L1; ~26 B/obs of Hinv / y_p per point not counted)
 }
 STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6}

@@ -76,6 +76,8 @@ typedef struct sba_options {
     double pcg_rel_tol;           /* relative tolerance of the reduced solve (sqrt(r.z / r0.z0)) */
     int32_t pcg_max_iters;        /* Ceres max_linear_solver_iterations = 500 */
     int32_t pcg_check_every;      /* host reads the convergence scalar every n PCG iterations (1 = exact oracle iteration count) */
+    int32_t operator_mode;        /* 0 = auto: factored camera pass of the Schur operator when every stiffness is identity
+                                     (rebuilds A, C from Pbar: 60 B/obs instead of 132 B/obs); 1 = always read the materialised A, C */
     int32_t verbose;
 } sba_options;
 

@@ -17,7 +17,7 @@ names = {0: "K1 residual+jacobian (cam order)", 1: "K1c cost only", 5: "K1p line
          8: "K2a point blocks", 9: "K2b camera blocks", 2: "K2 (a+b)", 4: "schur diag + invert",
          6: "matvec point pass", 7: "matvec camera pass", 3: "matvec S*x"}
 No = sz["n_obs"]
-bytes_per_obs = {0: 136, 1: 20 + 32, 5: 24 + 112, 8: 68, 9: 112, 2: 180, 6: 104, 7: 132, 3: 236}
+bytes_per_obs = {0: 136, 1: 20 + 32, 5: 24 + 112, 8: 68, 9: 112, 2: 180, 6: 104, 7: 60, 3: 164}
 out = {"shape": shape, "sizes": sz, "gen_s": t_gen, "ingest_s": t_fin, "stages": {}}
 for st in (0, 1, 5, 8, 9, 2, 4, 6, 7, 3):
     ms = s.time_stage(st, reps)

@@ -35,7 +35,7 @@ class SbaOptions(C.Structure):
         ("initial_radius", C.c_double), ("max_radius", C.c_double), ("min_radius", C.c_double),
         ("min_lm_diagonal", C.c_double), ("max_lm_diagonal", C.c_double), ("min_relative_decrease", C.c_double),
         ("jacobi_scaling", C.c_int32), ("pcg_rel_tol", C.c_double), ("pcg_max_iters", C.c_int32),
-        ("pcg_check_every", C.c_int32), ("verbose", C.c_int32),
+        ("pcg_check_every", C.c_int32), ("operator_mode", C.c_int32), ("verbose", C.c_int32),
     ]
 
 

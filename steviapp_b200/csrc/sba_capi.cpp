@@ -36,6 +36,7 @@ void sba_default_options(sba_options* o) {
     o->pcg_rel_tol = 1e-10;
     o->pcg_max_iters = 500;
     o->pcg_check_every = 1;
+    o->operator_mode = 0;
     o->verbose = 0;
 }
 

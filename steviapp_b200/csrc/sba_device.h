@@ -63,6 +63,8 @@ struct DevProblem {
     double* res;          // 2 planes of Ns   } camera order
     double* Cc;           // 6 planes of Ns   }   (d res / d rAxis)
     double* Ac;           // 6 planes of Ns   }   (d res / d X)
+    double* Pc;           // 3 planes of Ns: Pbar, or nullptr  } factored operator pass (identity stiffness):
+    double* Kc;           // 2 planes of Ns: Pi scale constants } A, C rebuilt from 40 B instead of read as 96 B
     double* qres;         // 2 planes of Nq   } point order
     double* qC;           // 6 planes of Nq   }
     double* qA;           // 6 planes of Nq   }

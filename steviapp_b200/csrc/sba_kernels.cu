@@ -71,10 +71,11 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
             for (int i = 0; i < 4; i++) W[i] = __ldg(P.obs_info + i * Ns + s);
             Wp = W;
         }
-        double r[2] = {0.0, 0.0}, Jc[12], Jp[6];
-        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp);
+        double r[2] = {0.0, 0.0}, Jc[12], Jp[6], aux[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp, (JAC && P.Pc) ? aux : nullptr);
         if (!ok) {
             bad = 1;
+            aux[0] = aux[1] = aux[2] = 0.0;   // Pbar = 0 marks a failed row for the factored pass
             r[0] = r[1] = 0.0;
             if (JAC) {
 #pragma unroll
@@ -93,6 +94,10 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
                 P.Cc[(size_t)(3 + j) * Ns + s] = Jc[6 + j];
                 P.Ac[(size_t)j * Ns + s] = Jp[j];
                 P.Ac[(size_t)(3 + j) * Ns + s] = Jp[3 + j];
+            }
+            if (P.Pc) {
+                P.Pc[s] = aux[0]; P.Pc[Ns + s] = aux[1]; P.Pc[2 * Ns + s] = aux[2];
+                if (P.Kc) { P.Kc[s] = aux[3]; P.Kc[Ns + s] = aux[4]; }
             }
         }
     }

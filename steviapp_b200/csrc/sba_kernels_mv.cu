@@ -39,6 +39,59 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
     for (int i = 0; i < 6; i++) { const double v = warp_sum(w[i]); if (lane == 0) out[i] = v; }
 }
 
+// ---------------------------------------------------------------------------
+// camera pass, FACTORED form (identity stiffness): with A = Pi R^T and C = Pi [Pbar]x Jr,
+//   Jc^T (A y) = [ -Jr^T (Pbar x n) ; -R n ],   n = Pi^T Pi (R^T y),
+// so a lane only needs Pbar (24 B, coalesced planes) [+ 16 B scale constants on spherical cameras],
+// the point index and the gathered y_p; Pi is rebuilt in registers (pi_from_pbar) and the per-camera
+// factors Jr^T, R are applied once per tile by lane 0.  60 B/obs instead of 132 B/obs.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProblem P) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
+    if (tile >= P.Nt) return;
+    const int cam = __ldg(P.tile_cam + tile);
+    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    const size_t Ns = (size_t)P.Ns;
+    const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+    double Rt[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) Rt[i] = __ldg(cc + i);   // warp-uniform addresses: one broadcast transaction each
+    const int spherical = P.cam_kind[cam];
+    const double f = __ldg(P.intr + 10 * __ldg(P.cam_model + cam));
+    double S1[3] = {0, 0, 0}, S2[3] = {0, 0, 0};
+    for (int s = start + lane; s < start + len; s += 32) {
+        const int pt = __ldg(P.obs_pt + s);
+        if (pt < 0) continue;
+        const double Px = __ldg(P.Pc + s), Py = __ldg(P.Pc + Ns + s), Pz = __ldg(P.Pc + 2 * Ns + s);
+        if (Px == 0.0 && Py == 0.0 && Pz == 0.0) continue;   // failed row (zero Jacobian)
+        const double2 y01 = ldg2(P.y_p + 4 * (size_t)pt), y23 = ldg2(P.y_p + 4 * (size_t)pt + 2);
+        double kx = f, ky = f;
+        if (spherical) { kx = __ldg(P.Kc + s); ky = __ldg(P.Kc + Ns + s); }
+        double p00, p02, p11, p12;
+        pi_from_pbar(Px, Py, Pz, kx, ky, spherical, &p00, &p02, &p11, &p12);
+        const double r0 = Rt[0] * y01.x + Rt[1] * y01.y + Rt[2] * y23.x;
+        const double r1 = Rt[3] * y01.x + Rt[4] * y01.y + Rt[5] * y23.x;
+        const double r2 = Rt[6] * y01.x + Rt[7] * y01.y + Rt[8] * y23.x;
+        const double b0 = p00 * r0 + p02 * r2, b1 = p11 * r1 + p12 * r2;      // b = A y
+        const double n0 = p00 * b0, n1 = p11 * b1, n2 = p02 * b0 + p12 * b1;  // n = Pi^T b
+        S2[0] += n0; S2[1] += n1; S2[2] += n2;
+        S1[0] += Py * n2 - Pz * n1; S1[1] += Pz * n0 - Px * n2; S1[2] += Px * n1 - Py * n0;   // Pbar x n
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) { S1[i] = warp_sum(S1[i]); S2[i] = warp_sum(S2[i]); }
+    if (lane == 0) {
+        double* out = P.tile_part + (size_t)TP * tile;
+        const double* Jr = cc + 12;
+        // C^T b summed = -Jr^T S1 ; -A^T b summed = -R S2 = -(Rt)^T S2
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            out[a] = -(__ldg(Jr + a) * S1[0] + __ldg(Jr + 3 + a) * S1[1] + __ldg(Jr + 6 + a) * S1[2]);
+            out[3 + a] = -(Rt[a] * S2[0] + Rt[3 + a] * S2[1] + Rt[6 + a] * S2[2]);
+        }
+    }
+}
+
 // thread per (camera, row):  out = -sum_tiles  [+ finish terms].  Fixed cameras: the sum is 0
 // (their Jc is zero in the reference's linearisation).
 // finish: out += hsign * (Hcc x)_row + damp * lam_c x + base
@@ -77,13 +130,15 @@ __global__ void k_camera_finish(DevProblem P, const double* x, const double* bas
     const int c = i / 6, a = i - 6 * c;
     out[i] += finish_terms(P, c, a, x, base, hsign, damp);
 }
+void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st) {
+    if (!P.Nt) return;
+    if (P.Pc) k_camera_pass_f<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    else k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+}
 void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, int damp, int finish,
                         double* out, cudaStream_t st) {
-    if (P.Nt) k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    launch_camera_pass_tiles(P, st);
     k_camera_reduce<<<cdiv(P.Nc * 6, 256), 256, 0, st>>>(P, x, base, hsign, damp, finish, out);
-}
-void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st) {
-    if (P.Nt) k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
 }
 void launch_camera_finish(const DevProblem& P, const double* x, const double* base, double hsign, int damp, double* out,
                           cudaStream_t st) {

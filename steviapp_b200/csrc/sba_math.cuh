@@ -99,10 +99,13 @@ SBA_HD void dir_from_uv(double u, double v, const double* in, double* d) {
 // One observation.  cc = camera cache record, X = point, d = view ray,
 // W = 2x2 stiffness (row-major) or nullptr (identity).
 // Outputs: res[2]; if JAC: Jc[12] = rows [d/dr(3) d/dt(3)], Jp[6] = rows d/dX(3).
+// aux (optional, 5 doubles): Pbar[3] and the two per-axis scale constants of Pi (plane: d_z, d_z;
+// spherical: (d_x^2+d_z^2)/d_z, (d_y^2+d_z^2)/d_z) -- everything the factored operator pass needs
+// to rebuild Pi, hence A = Pi R^T and C = Pi [Pbar]x Jr, without reading them.
 // Returns false when the plane cost sees Pbar.z < 0 (modularuvprojection.h:395-399).
 template <bool JAC>
 SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const double* W,
-                     int spherical, double* res, double* Jc, double* Jp) {
+                     int spherical, double* res, double* Jc, double* Jp, double* aux = nullptr) {
     const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
     const double Px = cc[0] * vx + cc[1] * vy + cc[2] * vz;
     const double Py = cc[3] * vx + cc[4] * vy + cc[5] * vz;
@@ -119,6 +122,7 @@ SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const d
         if (JAC) {
             const double s = d[2] * iz;
             p00 = s; p11 = s; p02 = -s * px; p12 = -s * py;
+            if (aux) { aux[3] = d[2]; aux[4] = d[2]; }
         }
     } else {
         // ":417-432": alpha1 = atan2(dx,dz), rotate (Pz,Px) by alpha1, angle of the result,
@@ -136,8 +140,10 @@ SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const d
             const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
             p00 = qx * Pz; p02 = -qx * Px;
             p11 = qy * Pz; p12 = -qy * Py;
+            if (aux) { aux[3] = kx; aux[4] = ky; }
         }
     }
+    if (JAC && aux) { aux[0] = Px; aux[1] = Py; aux[2] = Pz; }
     if (W) {
         res[0] = W[0] * e0 + W[1] * e1;
         res[1] = W[2] * e0 + W[3] * e1;
@@ -177,6 +183,20 @@ SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const d
         }
     }
     return true;
+}
+
+// Pi = d e / d Pbar rebuilt from Pbar and the aux scale constants (identity stiffness):
+// rows (p00, 0, p02), (0, p11, p12).  Same expressions as in obs_eval.
+SBA_HD void pi_from_pbar(double Px, double Py, double Pz, double kx, double ky, int spherical,
+                         double* p00, double* p02, double* p11, double* p12) {
+    if (!spherical) {
+        const double iz = 1.0 / Pz;
+        const double s = kx * iz;
+        *p00 = s; *p11 = s; *p02 = -s * (Px * iz); *p12 = -s * (Py * iz);
+    } else {
+        const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
+        *p00 = qx * Pz; *p02 = -qx * Px; *p11 = qy * Pz; *p12 = -qy * Py;
+    }
 }
 
 // symmetric 3x3 inverse by adjugate; H = (h00,h01,h02,h11,h12,h22) -> same packing.

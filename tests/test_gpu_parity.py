@@ -114,16 +114,26 @@ def test_normal_blocks(oracle, kw):
         assert relerr(g[k], o[k]) < 1e-11, k
 
 
-def test_schur_matvec_and_rhs(oracle):
-    sc = synthetic.make_scene("small")
+@pytest.mark.parametrize("kw", [dict(), dict(spherical=True), dict(mixed=True)])
+@pytest.mark.parametrize("operator_mode", [0, 1])
+def test_schur_matvec_and_rhs(oracle, kw, operator_mode):
+    """operator_mode 0 = factored camera pass (A, C rebuilt from Pbar), 1 = materialised A, C."""
+    sc = synthetic.make_scene("small", **kw)
     rng = np.random.default_rng(9)
     lam_c = rng.uniform(0.5, 2.0, (sc["n_cams"], 6)); lam_p = rng.uniform(0.5, 2.0, (sc["n_pts"], 3))
     x = rng.normal(size=(sc["n_cams"], 6))
     yo, ro = oracle.Problem(sc).schur_matvec(lam_c, lam_p, x)
-    s, _ = gpu_solver(sc)
+    s, _ = gpu_solver(sc, operator_mode=operator_mode)
     y, r = s.schur_matvec(lam_c, lam_p, x)
     assert relerr(y, yo) < 1e-11
     assert relerr(r, ro) < 1e-11
+
+
+def test_operator_modes_agree_on_lm():
+    sc = synthetic.make_scene("ladybug", mixed=True)
+    a = gpu_solver(sc, operator_mode=0)[0].solve(max_iterations=4, **FIXED_ITERS)
+    b = gpu_solver(sc, operator_mode=1)[0].solve(max_iterations=4, **FIXED_ITERS)
+    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-10 * b["final_cost"]
 
 
 @pytest.mark.parametrize("name", ["small_scene", "small_scene_spherical", "small_scene_mixed", "ladybug_scene"])
