@@ -52,6 +52,10 @@ __device__ __forceinline__ double block_max(double v, double* sh) {
 }
 
 __device__ __forceinline__ double2 ldg2(const double* p) { return __ldg(reinterpret_cast<const double2*>(p)); }
+// streaming (evict-first) variants for the big planes that are read/written once per pass, so that they do not
+// push the gathered per-point arrays (y_p, points, Hinv) out of the 126 MB L2
+__device__ __forceinline__ double2 ldcs2(const double* p) { return __ldcs(reinterpret_cast<const double2*>(p)); }
+__device__ __forceinline__ void stcs(double* p, double v) { __stcs(p, v); }
 __device__ __forceinline__ void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }

@@ -57,9 +57,9 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
     double acc = 0.0;
     int bad = 0;
     for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldg(P.obs_pt + s);
+        const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;   // padding slot: planes stay zero
-        const double2 uv = ldg2(P.obs_uv + 2 * (size_t)s);
+        const double2 uv = ldcs2(P.obs_uv + 2 * (size_t)s);
         const double2 x01 = ldg2(P.pts + 4 * (size_t)pt), x23 = ldg2(P.pts + 4 * (size_t)pt + 2);
         const double X[3] = {x01.x, x01.y, x23.x};
         double d[3];
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
         const double* Wp = nullptr;
         if (P.obs_info) {
 #pragma unroll
-            for (int i = 0; i < 4; i++) W[i] = __ldg(P.obs_info + i * Ns + s);
+            for (int i = 0; i < 4; i++) W[i] = __ldcs(P.obs_info + i * Ns + s);
             Wp = W;
         }
         double r[2] = {0.0, 0.0}, Jc[12], Jp[6], aux[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
@@ -86,18 +86,18 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
         }
         acc += r[0] * r[0] + r[1] * r[1];
         if (JAC) {
-            P.res[s] = r[0];
-            P.res[Ns + s] = r[1];
+            stcs(P.res + (s), r[0]);
+            stcs(P.res + (Ns + s), r[1]);
 #pragma unroll
             for (int j = 0; j < 3; j++) {
-                P.Cc[(size_t)j * Ns + s] = Jc[j];
-                P.Cc[(size_t)(3 + j) * Ns + s] = Jc[6 + j];
-                P.Ac[(size_t)j * Ns + s] = Jp[j];
-                P.Ac[(size_t)(3 + j) * Ns + s] = Jp[3 + j];
+                stcs(P.Cc + ((size_t)j * Ns + s), Jc[j]);
+                stcs(P.Cc + ((size_t)(3 + j) * Ns + s), Jc[6 + j]);
+                stcs(P.Ac + ((size_t)j * Ns + s), Jp[j]);
+                stcs(P.Ac + ((size_t)(3 + j) * Ns + s), Jp[3 + j]);
             }
             if (P.Pc) {
-                P.Pc[s] = aux[0]; P.Pc[Ns + s] = aux[1]; P.Pc[2 * Ns + s] = aux[2];
-                if (P.Kc) { P.Kc[s] = aux[3]; P.Kc[Ns + s] = aux[4]; }
+                stcs(P.Pc + (s), aux[0]); stcs(P.Pc + (Ns + s), aux[1]); stcs(P.Pc + (2 * Ns + s), aux[2]);
+                if (P.Kc) { stcs(P.Kc + (s), aux[3]); stcs(P.Kc + (Ns + s), aux[4]); }
             }
         }
     }

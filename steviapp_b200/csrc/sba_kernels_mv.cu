@@ -17,14 +17,14 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
     const size_t Ns = (size_t)P.Ns;
     double w[6] = {0, 0, 0, 0, 0, 0};
     for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldg(P.obs_pt + s);
+        const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
         const double2 y01 = ldg2(P.y_p + 4 * (size_t)pt), y23 = ldg2(P.y_p + 4 * (size_t)pt + 2);
         double A[6], C[6];
 #pragma unroll
         for (int a = 0; a < 6; a++) {
-            A[a] = __ldg(P.Ac + (size_t)a * Ns + s);
-            C[a] = __ldg(P.Cc + (size_t)a * Ns + s);
+            A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+            C[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
         }
         const double b0 = A[0] * y01.x + A[1] * y01.y + A[2] * y23.x;
         const double b1 = A[3] * y01.x + A[4] * y01.y + A[5] * y23.x;
@@ -61,13 +61,13 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
     const double f = __ldg(P.intr + 10 * __ldg(P.cam_model + cam));
     double S1[3] = {0, 0, 0}, S2[3] = {0, 0, 0};
     for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldg(P.obs_pt + s);
+        const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
-        const double Px = __ldg(P.Pc + s), Py = __ldg(P.Pc + Ns + s), Pz = __ldg(P.Pc + 2 * Ns + s);
+        const double Px = __ldcs(P.Pc + s), Py = __ldcs(P.Pc + Ns + s), Pz = __ldcs(P.Pc + 2 * Ns + s);
         if (Px == 0.0 && Py == 0.0 && Pz == 0.0) continue;   // failed row (zero Jacobian)
         const double2 y01 = ldg2(P.y_p + 4 * (size_t)pt), y23 = ldg2(P.y_p + 4 * (size_t)pt + 2);
         double kx = f, ky = f;
-        if (spherical) { kx = __ldg(P.Kc + s); ky = __ldg(P.Kc + Ns + s); }
+        if (spherical) { kx = __ldcs(P.Kc + s); ky = __ldcs(P.Kc + Ns + s); }
         double p00, p02, p11, p12;
         pi_from_pbar(Px, Py, Pz, kx, ky, spherical, &p00, &p02, &p11, &p12);
         const double r0 = Rt[0] * y01.x + Rt[1] * y01.y + Rt[2] * y23.x;

@@ -93,17 +93,17 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_schur_diag(DevProblem 
 #pragma unroll
     for (int i = 0; i < 21; i++) D[i] = 0.0;
     for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldg(P.obs_pt + s);
+        const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
         const double* Hp = P.Hinv + 8 * (size_t)pt;
         const double2 h01 = ldg2(Hp), h23 = ldg2(Hp + 2), h45 = ldg2(Hp + 4);
         double A[6], j0[6], j1[6];
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            A[a] = __ldg(P.Ac + (size_t)a * Ns + s);
-            A[3 + a] = __ldg(P.Ac + (size_t)(3 + a) * Ns + s);
-            j0[a] = __ldg(P.Cc + (size_t)a * Ns + s);
-            j1[a] = __ldg(P.Cc + (size_t)(3 + a) * Ns + s);
+            A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+            A[3 + a] = __ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
+            j0[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
+            j1[a] = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
             j0[3 + a] = -A[a];
             j1[3 + a] = -A[3 + a];
         }

@@ -159,19 +159,19 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
     for (int a = 0; a < 6; a++) x[a] = dc[6 * (size_t)cam + a];
     double acc = 0.0;
     for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldg(P.obs_pt + s);
+        const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
         const double2 d01 = ldg2(P.dp + 4 * (size_t)pt), d23 = ldg2(P.dp + 4 * (size_t)pt + 2);
         double m0 = 0.0, m1 = 0.0;
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            const double A0 = __ldg(P.Ac + (size_t)a * Ns + s), A1 = __ldg(P.Ac + (size_t)(3 + a) * Ns + s);
-            const double C0 = __ldg(P.Cc + (size_t)a * Ns + s), C1 = __ldg(P.Cc + (size_t)(3 + a) * Ns + s);
+            const double A0 = __ldcs(P.Ac + (size_t)a * Ns + s), A1 = __ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
+            const double C0 = __ldcs(P.Cc + (size_t)a * Ns + s), C1 = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
             const double dpa = a == 0 ? d01.x : (a == 1 ? d01.y : d23.x);
             m0 += C0 * x[a] + A0 * (dpa - x[3 + a]);
             m1 += C1 * x[a] + A1 * (dpa - x[3 + a]);
         }
-        const double r0 = __ldg(P.res + s), r1 = __ldg(P.res + Ns + s);
+        const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
         acc += m0 * (r0 + 0.5 * m0) + m1 * (r1 + 0.5 * m1);
     }
     acc = warp_sum(acc);

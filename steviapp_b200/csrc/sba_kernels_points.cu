@@ -38,9 +38,9 @@ __device__ __forceinline__ bool seg_head(int key, int lane) {
 __global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= P.Nq) return;
-    const int pt = __ldg(P.q_pt + q);
+    const int pt = __ldcs(P.q_pt + q);
     if (pt < 0) return;   // padding: planes stay zero
-    const int cam = __ldg(P.q_cam + q);
+    const int cam = __ldcs(P.q_cam + q);
     const double2 x01 = ldg2(P.pts + 4 * (size_t)pt), x23 = ldg2(P.pts + 4 * (size_t)pt + 2);
     const double X[3] = {x01.x, x01.y, x23.x};
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
@@ -51,13 +51,13 @@ __global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
     double intr[10];
 #pragma unroll
     for (int i = 0; i < 5; i++) { const double2 v = ldg2(in + 2 * i); intr[2 * i] = v.x; intr[2 * i + 1] = v.y; }
-    const double2 uv = ldg2(P.q_uv + 2 * (size_t)q);
+    const double2 uv = ldcs2(P.q_uv + 2 * (size_t)q);
     double d[3];
     dir_from_uv(uv.x, uv.y, intr, d);
     double W[4];
     const double* Wp = nullptr;
     if (P.q_info) {
-        const double2 w01 = ldg2(P.q_info + 4 * (size_t)q), w23 = ldg2(P.q_info + 4 * (size_t)q + 2);
+        const double2 w01 = ldcs2(P.q_info + 4 * (size_t)q), w23 = ldcs2(P.q_info + 4 * (size_t)q + 2);
         W[0] = w01.x; W[1] = w01.y; W[2] = w23.x; W[3] = w23.y;
         Wp = W;
     }
@@ -71,14 +71,14 @@ __global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
         for (int i = 0; i < 6; i++) Jp[i] = 0.0;
     }
     const size_t Nq = (size_t)P.Nq;
-    P.qres[q] = r[0];
-    P.qres[Nq + q] = r[1];
+    stcs(P.qres + (q), r[0]);
+    stcs(P.qres + (Nq + q), r[1]);
 #pragma unroll
     for (int j = 0; j < 3; j++) {
-        P.qC[(size_t)j * Nq + q] = Jc[j];
-        P.qC[(size_t)(3 + j) * Nq + q] = Jc[6 + j];
-        P.qA[(size_t)j * Nq + q] = Jp[j];
-        P.qA[(size_t)(3 + j) * Nq + q] = Jp[3 + j];
+        stcs(P.qC + ((size_t)j * Nq + q), Jc[j]);
+        stcs(P.qC + ((size_t)(3 + j) * Nq + q), Jc[6 + j]);
+        stcs(P.qA + ((size_t)j * Nq + q), Jp[j]);
+        stcs(P.qA + ((size_t)(3 + j) * Nq + q), Jp[3 + j]);
     }
 }
 void launch_linearize_points(const DevProblem& P, cudaStream_t st) {
@@ -106,14 +106,14 @@ __global__ void __launch_bounds__(256) k_point_blocks_q(DevProblem P) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;   // Nq is a multiple of 32: whole warps in range
     if (q >= P.Nq) return;
     const int lane = threadIdx.x & 31;
-    const int pt = __ldg(P.q_pt + q);
+    const int pt = __ldcs(P.q_pt + q);
     const size_t Nq = (size_t)P.Nq;
     double v[9];
     {
         double A[6];
 #pragma unroll
-        for (int a = 0; a < 6; a++) A[a] = __ldg(P.qA + (size_t)a * Nq + q);
-        const double r0 = __ldg(P.qres + q), r1 = __ldg(P.qres + Nq + q);
+        for (int a = 0; a < 6; a++) A[a] = __ldcs(P.qA + (size_t)a * Nq + q);
+        const double r0 = __ldcs(P.qres + q), r1 = __ldcs(P.qres + Nq + q);
         v[0] = A[0] * A[0] + A[3] * A[3]; v[1] = A[0] * A[1] + A[3] * A[4]; v[2] = A[0] * A[2] + A[3] * A[5];
         v[3] = A[1] * A[1] + A[4] * A[4]; v[4] = A[1] * A[2] + A[4] * A[5]; v[5] = A[2] * A[2] + A[5] * A[5];
         v[6] = A[0] * r0 + A[3] * r1; v[7] = A[1] * r0 + A[4] * r1; v[8] = A[2] * r0 + A[5] * r1;
@@ -173,17 +173,17 @@ __global__ void __launch_bounds__(256) k_point_pass_q(DevProblem P, const double
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= P.Nq) return;
     const int lane = threadIdx.x & 31;
-    const int pt = __ldg(P.q_pt + q);
+    const int pt = __ldcs(P.q_pt + q);
     const size_t Nq = (size_t)P.Nq;
     double u[3] = {0.0, 0.0, 0.0};
     if (pt >= 0) {
-        const double* xc = x + 6 * (size_t)__ldg(P.q_cam + q);
+        const double* xc = x + 6 * (size_t)__ldcs(P.q_cam + q);
         const double2 x01 = ldg2(xc), x23 = ldg2(xc + 2), x45 = ldg2(xc + 4);
         double A[6], C[6];
 #pragma unroll
         for (int a = 0; a < 6; a++) {
-            A[a] = __ldg(P.qA + (size_t)a * Nq + q);
-            C[a] = __ldg(P.qC + (size_t)a * Nq + q);
+            A[a] = __ldcs(P.qA + (size_t)a * Nq + q);
+            C[a] = __ldcs(P.qC + (size_t)a * Nq + q);
         }
         // rows of Jc x = C x_r - A x_t
         const double m0 = C[0] * x01.x + C[1] * x01.y + C[2] * x23.x - (A[0] * x23.y + A[1] * x45.x + A[2] * x45.y);

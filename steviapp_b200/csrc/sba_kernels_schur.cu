@@ -119,12 +119,12 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProbl
         double j0[6], j1[6];   // the two rows of Jc
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            j0[a] = __ldg(P.Cc + (size_t)a * Ns + s);
-            j1[a] = __ldg(P.Cc + (size_t)(3 + a) * Ns + s);
-            j0[3 + a] = -__ldg(P.Ac + (size_t)a * Ns + s);
-            j1[3 + a] = -__ldg(P.Ac + (size_t)(3 + a) * Ns + s);
+            j0[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
+            j1[a] = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
+            j0[3 + a] = -__ldcs(P.Ac + (size_t)a * Ns + s);
+            j1[3 + a] = -__ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
         }
-        const double r0 = __ldg(P.res + s), r1 = __ldg(P.res + Ns + s);
+        const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
         int q = 0;
 #pragma unroll
         for (int a = 0; a < 6; a++) {
