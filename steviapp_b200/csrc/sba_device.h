@@ -137,6 +137,7 @@ void launch_zero_fixed(const DevProblem& P, const double* x, double* xz, cudaStr
 void launch_negate(double* x, int n, cudaStream_t st);
 void launch_pcg_init(const DevProblem& P, cudaStream_t st);       // x=0, r=rhs, z=Minv r, p=z, rz, rz0
 int pcg_blocks(const DevProblem& P);
+bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st);   // A+B+C in one cooperative launch
 void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st);    // q (from tile partials or all-reduced) + p.q partials
 void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z | beta, p (frozen once converged)
 void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st);   // operator pass 2, tile partials only

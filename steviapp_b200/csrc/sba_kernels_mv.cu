@@ -46,7 +46,12 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
 // the point index and the gathered y_p; Pi is rebuilt in registers (pi_from_pbar) and the per-camera
 // factors Jr^T, R are applied once per tile by lane 0.  60 B/obs instead of 132 B/obs.
 // ---------------------------------------------------------------------------
+// The pass is latency-bound (dependent index -> gather chain), not byte-bound, so every lane first issues the
+// index loads of a batch of CPF_BATCH slots, then all their y_p gathers and Pbar loads, and only then does the math:
+// CPF_BATCH independent gathers in flight per lane instead of one.
+constexpr int CPF_BATCH = 4;
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProblem P) {
+    __shared__ double s_rt[WARPS_PER_BLOCK][10];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
     if (tile >= P.Nt) return;
@@ -54,29 +59,48 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
-    double Rt[9];
-#pragma unroll
-    for (int i = 0; i < 9; i++) Rt[i] = __ldg(cc + i);   // warp-uniform addresses: one broadcast transaction each
+    if (lane < 9) s_rt[warp][lane] = __ldg(cc + lane);
+    if (lane == 9) s_rt[warp][9] = __ldg(P.intr + 10 * __ldg(P.cam_model + cam));
+    __syncwarp();
+    const double* Rt = s_rt[warp];
     const int spherical = P.cam_kind[cam];
-    const double f = __ldg(P.intr + 10 * __ldg(P.cam_model + cam));
+    const double f = Rt[9];
     double S1[3] = {0, 0, 0}, S2[3] = {0, 0, 0};
-    for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldcs(P.obs_pt + s);
-        if (pt < 0) continue;
-        const double Px = __ldcs(P.Pc + s), Py = __ldcs(P.Pc + Ns + s), Pz = __ldcs(P.Pc + 2 * Ns + s);
-        if (Px == 0.0 && Py == 0.0 && Pz == 0.0) continue;   // failed row (zero Jacobian)
-        const double2 y01 = ldg2(P.y_p + 4 * (size_t)pt), y23 = ldg2(P.y_p + 4 * (size_t)pt + 2);
-        double kx = f, ky = f;
-        if (spherical) { kx = __ldcs(P.Kc + s); ky = __ldcs(P.Kc + Ns + s); }
-        double p00, p02, p11, p12;
-        pi_from_pbar(Px, Py, Pz, kx, ky, spherical, &p00, &p02, &p11, &p12);
-        const double r0 = Rt[0] * y01.x + Rt[1] * y01.y + Rt[2] * y23.x;
-        const double r1 = Rt[3] * y01.x + Rt[4] * y01.y + Rt[5] * y23.x;
-        const double r2 = Rt[6] * y01.x + Rt[7] * y01.y + Rt[8] * y23.x;
-        const double b0 = p00 * r0 + p02 * r2, b1 = p11 * r1 + p12 * r2;      // b = A y
-        const double n0 = p00 * b0, n1 = p11 * b1, n2 = p02 * b0 + p12 * b1;  // n = Pi^T b
-        S2[0] += n0; S2[1] += n1; S2[2] += n2;
-        S1[0] += Py * n2 - Pz * n1; S1[1] += Pz * n0 - Px * n2; S1[2] += Px * n1 - Py * n0;   // Pbar x n
+    for (int base = start + lane; base < start + len; base += 32 * CPF_BATCH) {
+        int pt[CPF_BATCH];
+#pragma unroll
+        for (int i = 0; i < CPF_BATCH; i++) {
+            const int s = base + 32 * i;
+            pt[i] = s < start + len ? __ldcs(P.obs_pt + s) : -1;
+        }
+        double2 y01[CPF_BATCH], y23[CPF_BATCH];
+        double Pb[CPF_BATCH][3], kk[CPF_BATCH][2];
+#pragma unroll
+        for (int i = 0; i < CPF_BATCH; i++) {
+            const int s = base + 32 * i;
+            if (pt[i] >= 0) {
+                y01[i] = ldg2(P.y_p + 4 * (size_t)pt[i]);
+                y23[i] = ldg2(P.y_p + 4 * (size_t)pt[i] + 2);
+                Pb[i][0] = __ldcs(P.Pc + s); Pb[i][1] = __ldcs(P.Pc + Ns + s); Pb[i][2] = __ldcs(P.Pc + 2 * Ns + s);
+                kk[i][0] = f; kk[i][1] = f;
+                if (spherical) { kk[i][0] = __ldcs(P.Kc + s); kk[i][1] = __ldcs(P.Kc + Ns + s); }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < CPF_BATCH; i++) {
+            if (pt[i] < 0) continue;
+            const double Px = Pb[i][0], Py = Pb[i][1], Pz = Pb[i][2];
+            if (Px == 0.0 && Py == 0.0 && Pz == 0.0) continue;   // failed row (zero Jacobian)
+            double p00, p02, p11, p12;
+            pi_from_pbar(Px, Py, Pz, kk[i][0], kk[i][1], spherical, &p00, &p02, &p11, &p12);
+            const double r0 = Rt[0] * y01[i].x + Rt[1] * y01[i].y + Rt[2] * y23[i].x;
+            const double r1 = Rt[3] * y01[i].x + Rt[4] * y01[i].y + Rt[5] * y23[i].x;
+            const double r2 = Rt[6] * y01[i].x + Rt[7] * y01[i].y + Rt[8] * y23[i].x;
+            const double b0 = p00 * r0 + p02 * r2, b1 = p11 * r1 + p12 * r2;      // b = A y
+            const double n0 = p00 * b0, n1 = p11 * b1, n2 = p02 * b0 + p12 * b1;  // n = Pi^T b
+            S2[0] += n0; S2[1] += n1; S2[2] += n2;
+            S1[0] += Py * n2 - Pz * n1; S1[1] += Pz * n0 - Px * n2; S1[2] += Px * n1 - Py * n0;   // Pbar x n
+        }
     }
 #pragma unroll
     for (int i = 0; i < 3; i++) { S1[i] = warp_sum(S1[i]); S2[i] = warp_sum(S2[i]); }

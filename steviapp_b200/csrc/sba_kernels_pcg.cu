@@ -7,6 +7,8 @@
 // The 6*Nc vectors are tiny (85 KB for 1778 cameras), so each update is ONE
 // single-block kernel: every dot product is a fixed-shape tree, bitwise
 // reproducible, and identical on every rank of a multi-GPU run.
+#include <cooperative_groups.h>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -134,7 +136,97 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_C(DevProblem P, double tol2, 
     if (i < n) P.pcg_p[i] = P.pcg_z[i] + beta * P.pcg_p[i];
     if (i == 0) { P.scalars[SC_RZ_NEXT] = rz_new; P.flags[FL_PCG_ITERS_NEXT] = P.flags[FL_PCG_ITERS] + 1; }
 }
+// A, B and C in ONE cooperative launch (two grid-wide barriers instead of two kernel boundaries): same arithmetic,
+// same trees, same freeze rule; used when the device can keep all pcg_blocks co-resident.
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, double tol2, int max_iters, int nb) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double sh[33];
+    __shared__ double sr[PCG_BLOCK];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
+    // ---- A (reads the scalars of the previous iteration through the NEXT copies: nobody writes them before the last barrier)
+    const double rz = P.scalars[SC_RZ_NEXT], rz0 = P.scalars[SC_RZ0];
+    const int it = P.flags[FL_PCG_ITERS_NEXT];
+    const bool frozen = !(rz > tol2 * rz0) || !(rz0 > 0.0) || it >= max_iters;
+    double pq = 0.0, p_i = 0.0, q_i = 0.0;
+    if (i < n) {
+        const int c = i / 6, a = i - 6 * c;
+        double acc = 0.0;
+        if (mode == 0) {
+            if (!P.cam_fixed[c]) {
+                const int t0 = P.cam_tile_off[c], t1 = P.cam_tile_off[c + 1];
+                for (int t = t0; t < t1; t++) acc += P.tile_part[(size_t)TP * t + a];
+            }
+            acc = -acc;
+        } else {
+            acc = P.pcg_q[i];
+        }
+        const double* H = P.Hcc + 21 * (size_t)c;
+        const double* p = P.pcg_p + 6 * (size_t)c;
+        double hx = 0.0;
+#pragma unroll
+        for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
+        p_i = p[a];
+        q_i = acc + (hx + P.lam_c[i] * p_i);
+        P.pcg_q[i] = q_i;
+        pq = p_i * q_i;
+    }
+    pq = block_sum(pq, sh);
+    if (threadIdx.x == 0) P.pcg_part[blockIdx.x] = pq;
+    if (frozen) return;   // uniform over the grid: no barrier is reached by anyone
+    grid.sync();
+    // ---- B
+    const double alpha = rz / fold_partials(P.pcg_part, nb, sh);
+    double r = 0.0;
+    if (i < n) {
+        P.pcg_x[i] += alpha * p_i;
+        r = P.pcg_r[i] - alpha * q_i;
+        P.pcg_r[i] = r;
+    }
+    sr[threadIdx.x] = r;
+    __syncthreads();
+    double rzp = 0.0, z = 0.0;
+    if (i < n) {
+        const int c = i / 6, a = i - 6 * c;
+        const double* M = P.Minv + 36 * (size_t)c + 6 * a;
+        const double* rc = sr + (threadIdx.x - a);
+#pragma unroll
+        for (int b = 0; b < 6; b++) z += M[b] * rc[b];
+        P.pcg_z[i] = z;
+        rzp = r * z;
+    }
+    rzp = block_sum(rzp, sh);
+    if (threadIdx.x == 0) P.pcg_part[nb + blockIdx.x] = rzp;
+    grid.sync();
+    // ---- C
+    const double rz_new = fold_partials(P.pcg_part + nb, nb, sh);
+    const double beta = rz_new / rz;
+    if (i < n) P.pcg_p[i] = z + beta * p_i;
+    grid.sync();   // every block has read SC_RZ_NEXT / FL_PCG_ITERS_NEXT before they are overwritten
+    if (i == 0) {
+        P.scalars[SC_RZ] = rz; P.flags[FL_PCG_ITERS] = it;
+        P.scalars[SC_RZ_NEXT] = rz_new; P.flags[FL_PCG_ITERS_NEXT] = it + 1;
+    }
+}
+
 int pcg_blocks(const DevProblem& P) { return cdiv(6 * P.Nc, PCG_BLOCK); }
+// returns false when the cooperative path is unavailable (caller falls back to A + B + C)
+bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st) {
+    static int ok_blocks = -1;
+    if (ok_blocks < 0) {
+        int dev = 0, coop = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_ABC, PCG_BLOCK, 0);
+        ok_blocks = coop ? sms * per_sm : 0;
+    }
+    int nb = pcg_blocks(P);
+    if (nb > ok_blocks) return false;
+    DevProblem Pc = P;
+    void* args[] = {&Pc, &mode, &tol2, &max_iters, &nb};
+    return cudaLaunchCooperativeKernel((void*)k_pcg_ABC, dim3(nb), dim3(PCG_BLOCK), args, 0, st) == cudaSuccess;
+}
 void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st) { k_pcg_A<<<pcg_blocks(P), PCG_BLOCK, 0, st>>>(P, mode); }
 void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t st) {
     const int nb = pcg_blocks(P);
