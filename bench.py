@@ -160,7 +160,8 @@ def bench_config(a):
 ALG_BYTES = {
     "k_residual_jacobian": 136,      # in 16 uv + 4 idx (+ point gather from L2), out 16 res + 48 C + 48 A   (J_t = -J_X form)
     "k_camera_pass": 60,             # factored form: 24 Pbar + 4 pt idx + 32 gathered y_p  (materialised form: 132)
-    "k_point_pass": 104,             # 48 C + 48 A planes + 4 pt idx + 4 cam idx (camera vector from L1; ~26 B/obs of Hinv / y_p per point not counted)
+    "k_point_pass": 56,              # 48 A planes + 4 pt idx + 4 cam idx; C x_r rebuilt as A((X-t) x R Jr x_r) (per-camera operand and the point
+                                     # from L1/L2; ~26 B/obs of Hinv / y_p per point not counted)
 }
 STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6}
 

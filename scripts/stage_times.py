@@ -13,13 +13,13 @@ t0 = time.time(); sc = synthetic.make_scene(shape); t_gen = time.time() - t0
 s = SBASolver(pcg_check_every=8)
 t0 = time.time(); synthetic.load_into(s, sc); s.finalize(); t_fin = time.time() - t0
 sz = s.sizes()
-names = {0: "K1 residual+jacobian (cam order)", 1: "K1c cost only", 5: "K1p linearize (point order)",
-         8: "K2a point blocks", 9: "K2b camera blocks", 2: "K2 (a+b)", 4: "schur diag + invert",
+names = {0: "K1 residual+jacobian (cam order)", 1: "K1c cost only", 5: "K1p+K2a linearize + point blocks",
+         9: "K2b camera blocks", 2: "K1p+K2a+K2b", 4: "schur diag + invert",
          6: "matvec point pass", 7: "matvec camera pass", 3: "matvec S*x"}
 No = sz["n_obs"]
-bytes_per_obs = {0: 136, 1: 20 + 32, 5: 24 + 112, 8: 68, 9: 112, 2: 180, 6: 104, 7: 60, 3: 164}
+bytes_per_obs = {0: 136, 1: 20 + 32, 5: 24 + 48 + 19, 9: 112, 2: 24 + 48 + 19 + 112, 6: 56, 7: 60, 3: 116}
 out = {"shape": shape, "sizes": sz, "gen_s": t_gen, "ingest_s": t_fin, "stages": {}}
-for st in (0, 1, 5, 8, 9, 2, 4, 6, 7, 3):
+for st in (0, 1, 5, 9, 2, 4, 6, 7, 3):
     ms = s.time_stage(st, reps)
     gbs = bytes_per_obs.get(st, 0) * No / (ms * 1e-3) / 1e9 if st in bytes_per_obs else None
     out["stages"][names[st]] = {"ms": ms, "GB/s(alg)": gbs, "Mobs/s": No / ms / 1e3}

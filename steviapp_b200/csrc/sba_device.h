@@ -19,11 +19,14 @@ constexpr int TP = 28;               // doubles per tile partial
 //
 // The Jacobian is stored compressed: for every observation
 //   A = d res / d X (2x3)  and  C = d res / d rAxis (2x3);   d res / d t = -A exactly,
-// so Jc = [C | -A], Jp = A.  It is kept twice, once per traversal order:
-//   camera order : SoA planes res[2], C[6], A[6] over slots   (coalesced warp-per-tile passes)
-//   point order  : SoA planes qres[2], qC[6], qA[6] over q slots (thread-per-slot passes, segmented warp reductions)
+// so Jc = [C | -A], Jp = A.
+//   camera order : SoA planes res[2], C[6], A[6] over slots   (coalesced warp-per-tile / thread-per-slot passes)
+//   point order  : SoA planes qA[6] over q slots (thread-per-slot passes, segmented warp reductions)
 struct DevProblem {
     int32_t Nc, Np, No, Ns, Nt, Nm, Nprior;
+    int32_t cp_variant;   // camera pass (factored): gathers in flight per lane 0 -> 2 (default), 1 -> 4, 2 -> 1 (measurement knob)
+    int32_t pp_variant;   // point pass: 0 = shared-memory operand table when it fits, 1 = always gather from global
+    double center[3];     // fixed reference position (mean camera position at finalize) of the point-pass operand
     // cameras (replicated on every rank)
     double* cam_r;        // 3*Nc AoS (PoseNode::rAxis)
     double* cam_t;        // 3*Nc AoS
@@ -65,9 +68,8 @@ struct DevProblem {
     double* Ac;           // 6 planes of Ns   }   (d res / d X)
     double* Pc;           // 3 planes of Ns: Pbar, or nullptr  } factored operator pass (identity stiffness):
     double* Kc;           // 2 planes of Ns: Pi scale constants } A, C rebuilt from 40 B instead of read as 96 B
-    double* qres;         // 2 planes of Nq   } point order
-    double* qC;           // 6 planes of Nq   }
-    double* qA;           // 6 planes of Nq   }
+    double* qA;           // 6 planes of Nq: point order.  C is NOT kept in point order: C x_r = A ((X - t) x (R Jr x_r)),
+                          // so the point pass needs only A, the point and a 9-double per-camera operand (cam_vec)
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -90,6 +92,8 @@ struct DevProblem {
     double* scale_p;      // 4*Np AoS
     // work vectors
     double* tile_part;    // TP*Nt tile partials
+    double* mv_part;      // 6 per tile: camera-pass partial of the tile, per-camera factors already applied
+    double* cam_vec;      // 8*Nc: operand of the point pass, (a_c = R Jr x_r, g_c = x_t + (t - center) x a_c, pad) for the current x
     double* tile_cost;    // Nt
     double* y_p;          // 4*Np AoS point-side temporary of the implicit operator
     double* dp;           // 4*Np AoS step of the points
@@ -112,11 +116,10 @@ enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, F
 // ---- launch wrappers (sba_kernels.cu); all asynchronous on `st` ----
 void launch_pose_cache(const DevProblem& P, cudaStream_t st);
 void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st);   // K1 / K1c, camera order
-void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p: point-order planes
+void launch_linearize_points(const DevProblem& P, cudaStream_t st);              // K1p+K2a: point-order A planes, Hpp, gp
 void launch_prior_eval(const DevProblem& P, int store, cudaStream_t st);         // prior residuals (stored if store) + their cost
 void launch_pack_tail(const DevProblem& P, double* tail, cudaStream_t st);
 void launch_cost_reduce(const DevProblem& P, cudaStream_t st);                   // tile costs -> SC_COST_OBS
-void launch_point_blocks(const DevProblem& P, cudaStream_t st);                  // K2a: Hpp, gp
 void launch_camera_blocks(const DevProblem& P, cudaStream_t st);                 // K2b: tile partials + per-camera reduce -> Hcc, gc
 void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st);     // add A^T A, A^T r of the priors
 void launch_scaling(const DevProblem& P, int enabled, cudaStream_t st);
@@ -126,7 +129,9 @@ void launch_schur_diag(const DevProblem& P, cudaStream_t st);                   
 void launch_schur_diag_invert(const DevProblem& P, cudaStream_t st);             // Minv = (Hcc + lam - Sd)^-1
 // implicit operator pieces.  mode 0: y_p = Hinv * sum Jp^T Jc x ; mode 1: y_p = Hinv gp ;
 // mode 2: dp = -(Hinv (gp + sum Jp^T Jc x))
-void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st);
+// table_ready: cam_vec already holds the operand of x (the PCG kernels refresh it whenever they update p)
+void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st, bool table_ready = false);
+void launch_cam_vec(const DevProblem& P, const double* x, cudaStream_t st);
 // out = -sum_o Jc^T Jp y_p (fixed cameras: 0); if finish: out += hsign * (Hcc x) + damp * lam_c .* x + base.
 // Multi-GPU runs all-reduce the partial first and call launch_camera_finish afterwards.
 void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, int damp, int finish,

@@ -22,6 +22,7 @@ __global__ void k_pose_cache(DevProblem P) {
     if (c >= P.Nc) return;
     double out[CAM_CACHE_STRIDE];
     pose_cache(P.cam_r + 3 * c, P.cam_t + 3 * c, out);
+    out[21] = P.intr[10 * P.cam_model[c]];   // f of the camera's model: d_z of the plane cost (factored camera pass)
 #pragma unroll
     for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
 }

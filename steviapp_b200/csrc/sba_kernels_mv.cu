@@ -19,22 +19,22 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
     for (int s = start + lane; s < start + len; s += 32) {
         const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
-        const double2 y01 = ldg2(P.y_p + 4 * (size_t)pt), y23 = ldg2(P.y_p + 4 * (size_t)pt + 2);
+        const d4 y = ld256(P.y_p + 4 * (size_t)pt);
         double A[6], C[6];
 #pragma unroll
         for (int a = 0; a < 6; a++) {
             A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
             C[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
         }
-        const double b0 = A[0] * y01.x + A[1] * y01.y + A[2] * y23.x;
-        const double b1 = A[3] * y01.x + A[4] * y01.y + A[5] * y23.x;
+        const double b0 = A[0] * y.x + A[1] * y.y + A[2] * y.z;
+        const double b1 = A[3] * y.x + A[4] * y.y + A[5] * y.z;
 #pragma unroll
         for (int a = 0; a < 3; a++) {
             w[a] += C[a] * b0 + C[3 + a] * b1;
             w[3 + a] -= A[a] * b0 + A[3 + a] * b1;
         }
     }
-    double* out = P.tile_part + (size_t)TP * tile;
+    double* out = P.mv_part + 6 * (size_t)tile;
 #pragma unroll
     for (int i = 0; i < 6; i++) { const double v = warp_sum(w[i]); if (lane == 0) out[i] = v; }
 }
@@ -49,8 +49,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
 // The pass is latency-bound (dependent index -> gather chain), not byte-bound, so every lane first issues the
 // index loads of a batch of CPF_BATCH slots, then all their y_p gathers and Pbar loads, and only then does the math:
 // CPF_BATCH independent gathers in flight per lane instead of one.
-constexpr int CPF_BATCH = 4;
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProblem P) {
+template <int CPF_BATCH>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, CPF_BATCH >= 4 ? 3 : (CPF_BATCH == 2 ? 4 : 6)) k_camera_pass_f(DevProblem P) {
     __shared__ double s_rt[WARPS_PER_BLOCK][10];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
     const size_t Ns = (size_t)P.Ns;
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
     if (lane < 9) s_rt[warp][lane] = __ldg(cc + lane);
-    if (lane == 9) s_rt[warp][9] = __ldg(P.intr + 10 * __ldg(P.cam_model + cam));
+    if (lane == 9) s_rt[warp][9] = __ldg(cc + 21);   // f of the camera's model (written by K0): d_z of the plane cost
     __syncwarp();
     const double* Rt = s_rt[warp];
     const int spherical = P.cam_kind[cam];
@@ -73,14 +73,13 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
             const int s = base + 32 * i;
             pt[i] = s < start + len ? __ldcs(P.obs_pt + s) : -1;
         }
-        double2 y01[CPF_BATCH], y23[CPF_BATCH];
+        d4 y[CPF_BATCH];
         double Pb[CPF_BATCH][3], kk[CPF_BATCH][2];
 #pragma unroll
         for (int i = 0; i < CPF_BATCH; i++) {
             const int s = base + 32 * i;
             if (pt[i] >= 0) {
-                y01[i] = ldg2(P.y_p + 4 * (size_t)pt[i]);
-                y23[i] = ldg2(P.y_p + 4 * (size_t)pt[i] + 2);
+                y[i] = ld256(P.y_p + 4 * (size_t)pt[i]);   // one 256-bit gather per observation
                 Pb[i][0] = __ldcs(P.Pc + s); Pb[i][1] = __ldcs(P.Pc + Ns + s); Pb[i][2] = __ldcs(P.Pc + 2 * Ns + s);
                 kk[i][0] = f; kk[i][1] = f;
                 if (spherical) { kk[i][0] = __ldcs(P.Kc + s); kk[i][1] = __ldcs(P.Kc + Ns + s); }
@@ -93,9 +92,9 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
             if (Px == 0.0 && Py == 0.0 && Pz == 0.0) continue;   // failed row (zero Jacobian)
             double p00, p02, p11, p12;
             pi_from_pbar(Px, Py, Pz, kk[i][0], kk[i][1], spherical, &p00, &p02, &p11, &p12);
-            const double r0 = Rt[0] * y01[i].x + Rt[1] * y01[i].y + Rt[2] * y23[i].x;
-            const double r1 = Rt[3] * y01[i].x + Rt[4] * y01[i].y + Rt[5] * y23[i].x;
-            const double r2 = Rt[6] * y01[i].x + Rt[7] * y01[i].y + Rt[8] * y23[i].x;
+            const double r0 = Rt[0] * y[i].x + Rt[1] * y[i].y + Rt[2] * y[i].z;
+            const double r1 = Rt[3] * y[i].x + Rt[4] * y[i].y + Rt[5] * y[i].z;
+            const double r2 = Rt[6] * y[i].x + Rt[7] * y[i].y + Rt[8] * y[i].z;
             const double b0 = p00 * r0 + p02 * r2, b1 = p11 * r1 + p12 * r2;      // b = A y
             const double n0 = p00 * b0, n1 = p11 * b1, n2 = p02 * b0 + p12 * b1;  // n = Pi^T b
             S2[0] += n0; S2[1] += n1; S2[2] += n2;
@@ -105,7 +104,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
 #pragma unroll
     for (int i = 0; i < 3; i++) { S1[i] = warp_sum(S1[i]); S2[i] = warp_sum(S2[i]); }
     if (lane == 0) {
-        double* out = P.tile_part + (size_t)TP * tile;
+        double* out = P.mv_part + 6 * (size_t)tile;
         const double* Jr = cc + 12;
         // C^T b summed = -Jr^T S1 ; -A^T b summed = -R S2 = -(Rt)^T S2
 #pragma unroll
@@ -116,7 +115,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass_f(DevProbl
     }
 }
 
-// thread per (camera, row):  out = -sum_tiles  [+ finish terms].  Fixed cameras: the sum is 0
+// thread per (camera, row):  out = -sum of the camera's tile partials  [+ finish terms].  Fixed cameras: the sum is 0
 // (their Jc is zero in the reference's linearisation).
 // finish: out += hsign * (Hcc x)_row + damp * lam_c x + base
 __device__ __forceinline__ double finish_terms(const DevProblem& P, int c, int a, const double* x, const double* base,
@@ -141,8 +140,7 @@ __global__ void k_camera_reduce(DevProblem P, const double* x, const double* bas
     const int c = i / 6, a = i - 6 * c;
     double acc = 0.0;
     if (!P.cam_fixed[c]) {
-        const int t0 = P.cam_tile_off[c], t1 = P.cam_tile_off[c + 1];
-        for (int t = t0; t < t1; t++) acc += P.tile_part[(size_t)TP * t + a];
+        acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
     }
     acc = -acc;
     if (finish) acc += finish_terms(P, c, a, x, base, hsign, damp);
@@ -156,7 +154,12 @@ __global__ void k_camera_finish(DevProblem P, const double* x, const double* bas
 }
 void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st) {
     if (!P.Nt) return;
-    if (P.Pc) k_camera_pass_f<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    if (P.Pc) {
+        const int nb = cdiv(P.Nt, WARPS_PER_BLOCK);
+        if (P.cp_variant == 1) k_camera_pass_f<4><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
+        else if (P.cp_variant == 2) k_camera_pass_f<1><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
+        else k_camera_pass_f<2><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);   // measured best on B200 (Venice shape)
+    }
     else k_camera_pass<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
 }
 void launch_camera_pass(const DevProblem& P, const double* x, const double* base, double hsign, int damp, int finish,

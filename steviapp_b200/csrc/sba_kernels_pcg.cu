@@ -34,11 +34,12 @@ __global__ void __launch_bounds__(RED_BLOCK) k_pcg_init(DevProblem P) {
         P.pcg_x[i] = 0.0; P.pcg_r[i] = r; P.pcg_z[i] = z; P.pcg_p[i] = z;
         acc += r * z;
     }
-    acc = block_sum(acc, sh);
+    acc = block_sum(acc, sh);   // (contains __syncthreads: every p of this block is visible below)
     if (threadIdx.x == 0) {
         P.scalars[SC_RZ] = acc; P.scalars[SC_RZ_NEXT] = acc; P.scalars[SC_RZ0] = acc;
         P.flags[FL_PCG_ITERS] = 0; P.flags[FL_PCG_ITERS_NEXT] = 0;
     }
+    for (int cam = threadIdx.x; cam < P.Nc; cam += blockDim.x) cam_vec_store(P, cam, P.pcg_p + 6 * (size_t)cam);   // operand of the first point pass
 }
 void launch_pcg_init(const DevProblem& P, cudaStream_t st) { k_pcg_init<<<1, RED_BLOCK, 0, st>>>(P); }
 
@@ -78,8 +79,7 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_A(DevProblem P, int mode) {
         double acc = 0.0;
         if (mode == 0) {
             if (!P.cam_fixed[c]) {
-                const int t0 = P.cam_tile_off[c], t1 = P.cam_tile_off[c + 1];
-                for (int t = t0; t < t1; t++) acc += P.tile_part[(size_t)TP * t + a];
+                acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
             }
             acc = -acc;
         } else {
@@ -128,12 +128,17 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_B(DevProblem P, double tol2, 
 }
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_C(DevProblem P, double tol2, int max_iters, int nb) {
     __shared__ double sh[33];
+    __shared__ double sp[PCG_BLOCK];
     if (pcg_frozen(P, tol2, max_iters)) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
     const double rz = P.scalars[SC_RZ];
     const double rz_new = fold_partials(P.pcg_part + nb, nb, sh);
     const double beta = rz_new / rz;
-    if (i < n) P.pcg_p[i] = P.pcg_z[i] + beta * P.pcg_p[i];
+    double pn = 0.0;
+    if (i < n) { pn = P.pcg_z[i] + beta * P.pcg_p[i]; P.pcg_p[i] = pn; }
+    sp[threadIdx.x] = pn;
+    __syncthreads();
+    if (i < n && i % 6 == 0) cam_vec_store(P, i / 6, sp + threadIdx.x);   // operand of the next point pass (PCG_BLOCK % 6 == 0)
     if (i == 0) { P.scalars[SC_RZ_NEXT] = rz_new; P.flags[FL_PCG_ITERS_NEXT] = P.flags[FL_PCG_ITERS] + 1; }
 }
 // A, B and C in ONE cooperative launch (two grid-wide barriers instead of two kernel boundaries): same arithmetic,
@@ -154,8 +159,7 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
         double acc = 0.0;
         if (mode == 0) {
             if (!P.cam_fixed[c]) {
-                const int t0 = P.cam_tile_off[c], t1 = P.cam_tile_off[c + 1];
-                for (int t = t0; t < t1; t++) acc += P.tile_part[(size_t)TP * t + a];
+                acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
             }
             acc = -acc;
         } else {
@@ -201,7 +205,11 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
     // ---- C
     const double rz_new = fold_partials(P.pcg_part + nb, nb, sh);
     const double beta = rz_new / rz;
-    if (i < n) P.pcg_p[i] = z + beta * p_i;
+    const double pn = z + beta * p_i;
+    if (i < n) P.pcg_p[i] = pn;
+    sr[threadIdx.x] = pn;   // (sr was last read before the block_sum barriers of phase B)
+    __syncthreads();
+    if (i < n && i % 6 == 0) cam_vec_store(P, i / 6, sr + threadIdx.x);   // operand of the next point pass (PCG_BLOCK % 6 == 0)
     grid.sync();   // every block has read SC_RZ_NEXT / FL_PCG_ITERS_NEXT before they are overwritten
     if (i == 0) {
         P.scalars[SC_RZ] = rz; P.flags[FL_PCG_ITERS] = it;
