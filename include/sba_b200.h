@@ -76,8 +76,14 @@ typedef struct sba_options {
     double pcg_rel_tol;           /* relative tolerance of the reduced solve (sqrt(r.z / r0.z0)) */
     int32_t pcg_max_iters;        /* Ceres max_linear_solver_iterations = 500 */
     int32_t pcg_check_every;      /* host reads the convergence scalar every n PCG iterations (1 = exact oracle iteration count) */
-    int32_t operator_mode;        /* 0 = auto: factored camera pass of the Schur operator when every stiffness is identity
-                                     (rebuilds A, C from Pbar: 60 B/obs instead of 132 B/obs); 1 = always read the materialised A, C */
+    int32_t operator_mode;        /* reduced camera system S inside the PCG.
+                                     0 = auto: EXPLICIT S (dense 384x384 tiles over the upper block triangle, built per LM
+                                         iteration from static contribution slots) when its tiles are a smaller stream than the
+                                         implicit passes, it fits in HBM and the run is single-GPU; else implicit as in 2;
+                                     1 = implicit operator reading the materialised A, C (132 B/obs camera pass);
+                                     2 = implicit operator, factored camera pass when every stiffness is identity
+                                         (rebuilds A, C from Pbar: 60 B/obs), else as 1;
+                                     3 = explicit S forced (error if it cannot be built) */
     int32_t verbose;
 } sba_options;
 

@@ -70,6 +70,32 @@ struct DevProblem {
     double* Kc;           // 2 planes of Ns: Pi scale constants } A, C rebuilt from 40 B instead of read as 96 B
     double* qA;           // 6 planes of Nq: point order.  C is NOT kept in point order: C x_r = A ((X - t) x (R Jr x_r)),
                           // so the point pass needs only A, the point and a 9-double per-camera operand (cam_vec)
+    // ---- explicit reduced camera system (operator_mode 0 auto / 3 forced; see sba_kernels_explicit.cu) ----
+    // S is kept as dense 384x384 tiles (64 cameras x 64 cameras) over the UPPER block triangle: tile (I,J), I <= J, holds
+    // the 6x6 blocks S_ij, i in I, j in J, i < j; diagonal tiles hold S_ii / 2 on their diagonal and zeros below, so
+    // y_I += T x_J, y_J += T^T x_I reproduces the symmetric product with ONE read of every stored byte.
+    int32_t ex_on;        // 1: PCG applies S from the tiles
+    int32_t ex_NT;        // camera tiles per dimension = ceil(Nc / 64)
+    int32_t ex_ntiles;    // allocated (non-empty) tiles
+    int32_t ex_nblocks;   // off-diagonal blocks (i < j) with at least one common point
+    int32_t ex_ncontrib;  // point-pair contributions: sum_p k_p (k_p - 1) / 2
+    int32_t* ex_tile_of;  // ex_NT * ex_NT: tile index of (I,J), I <= J, or -1
+    int32_t* ex_tile_I;   // ex_ntiles
+    int32_t* ex_tile_J;   // ex_ntiles
+    double* ex_S;         // ex_ntiles * 384 * 384, row-major tiles
+    int32_t* ex_qa;       // ex_ncontrib: q slot of the first observation (smaller camera index), producer (point) order
+    int32_t* ex_qb;       // ex_ncontrib: q slot of the second observation
+    int32_t* ex_dest;     // ex_ncontrib: position of the contribution in block-sorted order
+    int32_t* ex_blk_i;    // ex_nblocks
+    int32_t* ex_blk_j;    // ex_nblocks
+    int32_t* ex_blk_off;  // ex_nblocks: first contribution of the block in the block-sorted buffer
+    int32_t* ex_blk_len;  // ex_nblocks: run length; the block list is ordered by run length, longest first
+    double* ex_contrib;   // 12 * ex_ncontrib: compact contributions (K 3x3, X), block-sorted; expanded to D_i K D_j^T by the assembly
+    double* ex_row;       // ex_ntiles * 384: row partials of the tile mat-vec (y_I += T x_J)
+    double* ex_col;       // ex_ntiles * 6 * 384: column partials per 64-row chunk (y_J += T^T x_I); = ex_row + ex_ntiles * 384
+    int32_t* ex_fold_ptr; // ex_NT + 1
+    int32_t* ex_fold_off; // offsets (doubles, relative to ex_row) of the partial vectors of every camera tile, fixed order
+    double* cam_Q;        // 12*Nc: Q = (R Jr)^T row-major (9) + pad, written by K0: C = A [X - t]x Q^T
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -156,6 +182,10 @@ void launch_unpack_blocks(const DevProblem& P, double* Hcc36, double* Hpp9, doub
 void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* lam_p3, cudaStream_t st);
 void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st);
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
+// explicit reduced camera system
+void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> tiles (needs Hinv, Sd, lam_c of this LM iteration)
+void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st);   // tile partials ex_row / ex_col of S x
+void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);
 

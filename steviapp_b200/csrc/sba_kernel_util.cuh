@@ -130,4 +130,37 @@ __device__ __forceinline__ void cam_vec_store(const DevProblem& P, int c, const 
     st2(o + 6, 0.0, 0.0);
 }
 
+// ---- explicit reduced camera system (sba_kernels_explicit.cu): tile geometry and the fold of the mat-vec partials
+constexpr int EX_TB = 64;            // cameras per tile side
+constexpr int EX_TD = 6 * EX_TB;     // 384 scalars per tile side
+constexpr int EX_CHUNK = 64;         // rows per mat-vec CTA
+constexpr int EX_NCHUNK = EX_TD / EX_CHUNK;
+
+// y = S x from the partials, element i of camera tile K: the static list ex_fold_off[ex_fold_ptr[K] .. ex_fold_ptr[K+1])
+// holds the offsets (relative to ex_row) of the partial vectors that contribute to tile K -- row partials of the tiles
+// (K, J >= K) in J order, then the column partials of the tiles (I <= K, K) in (I, chunk) order.  Block-cooperative:
+// all threads of the block belong to ONE camera tile (EX_TD % blockDim.x == 0); the offsets are staged in shared memory
+// so the ~200 loads of a thread are independent and pipeline.  Four interleaved chains combined in a fixed order ->
+// deterministic.  Every thread of the block must call it (barriers inside); `valid` = the thread owns element i.
+__device__ __forceinline__ double explicit_fold(const DevProblem& P, int i, bool valid, int* s_off /* blockDim.x ints */) {
+    const int K = (blockIdx.x * blockDim.x) / EX_TD, e = i - K * EX_TD;
+    const int m0 = __ldg(P.ex_fold_ptr + K), m1 = __ldg(P.ex_fold_ptr + K + 1);
+    const double* base = P.ex_row + e;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    for (int mb = m0; mb < m1; mb += blockDim.x) {
+        __syncthreads();
+        if (mb + (int)threadIdx.x < m1) s_off[threadIdx.x] = __ldg(P.ex_fold_off + mb + threadIdx.x);
+        __syncthreads();
+        const int n = min((int)blockDim.x, m1 - mb);
+        if (valid) {
+            int m = 0;
+            for (; m + 3 < n; m += 4) {
+                a0 += base[s_off[m]]; a1 += base[s_off[m + 1]]; a2 += base[s_off[m + 2]]; a3 += base[s_off[m + 3]];
+            }
+            for (; m < n; m++) a0 += base[s_off[m]];
+        }
+    }
+    return (a0 + a1) + (a2 + a3);
+}
+
 }  // namespace sba

@@ -25,6 +25,13 @@ __global__ void k_pose_cache(DevProblem P) {
     out[21] = P.intr[10 * P.cam_model[c]];   // f of the camera's model: d_z of the plane cost (factored camera pass)
 #pragma unroll
     for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
+    // Q = (R Jr)^T: C = A [X - t]x Q^T (explicit reduced system, sba_kernels_explicit.cu).  R[i][k] = Rt[3k+i]
+    double* Q = P.cam_Q + 12 * (size_t)c;
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int a = 0; a < 3; a++) Q[3 * r + a] = out[a] * out[12 + r] + out[3 + a] * out[15 + r] + out[6 + a] * out[18 + r];
+    Q[9] = Q[10] = Q[11] = 0.0;
 }
 void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
     k_pose_cache<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);

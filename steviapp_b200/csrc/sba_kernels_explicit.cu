@@ -1,0 +1,257 @@
+// sba_kernels_explicit.cu -- the EXPLICIT reduced camera system
+//   S = (Hcc + Dc) - sum_p W_p (Hpp + Dp)^-1 W_p^T,   W_o = Jc_o^T A_o  (6x3)
+// (Ceres SchurEliminator behind modularsbasolver.cpp:938; g2o analogue block_solver.hpp:371-447),
+// kept as dense 384x384 tiles over the upper block triangle, and its mat-vec for the PCG.
+//
+// Why: one application of the implicit operator streams every observation twice and is bound by gathers
+// (L1 wavefronts), 150 times per LM iteration.  When the co-visibility graph is dense (Venice: 69 % of the
+// camera pairs share a point) the tiles are SMALLER than the observation planes and their mat-vec is a pure
+// coalesced stream that reads every stored byte once (symmetric storage).
+//
+// Determinism (no floating-point atomics): every (point, observation pair) contribution has a STATIC slot in a
+// block-sorted buffer (finalize builds the list); the assembly kernel sums the run of a block in buffer order.
+//
+// Algebra: with d = X - t, Q = (R Jr)^T and C = A [d]x Q^T (see sba_kernels_points.cu),
+//   W_o = T_c D_o (A_o^T A_o),  T_c = diag(Q_c, I),  D_o = [ [d_o]x^T ; -I ]  (6x3)
+//   W_i Hinv W_j^T = T_i ( D_i K D_j^T ) T_j^T,   K = A_i^T (A_i Hinv A_j^T) A_j   (3x3)
+// so a contribution needs only the point-order A planes, the point, Hinv and the two camera centres; the
+// per-camera factors T are applied once per block by the assembly kernel.
+#include <algorithm>
+
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+// ---------------------------------------------------------------------------
+// producer: one thread per contribution, point order (neighbouring threads share the point, Hinv and most A rows:
+// the gathers hit L1).  Writes the COMPACT contribution (K 3x3, X) = 12 doubles = 96 B = three whole sectors to its
+// static slot; the 6x6 block D_i K D_j^T = [ -U [dj]x , U ; -K [dj]x , K ], U = [di]x K, d = X - t, is expanded by the
+// assembly kernel, where t_i and t_j are per-block constants (3x less traffic than storing the 36 entries).
+// ---------------------------------------------------------------------------
+constexpr int EX_CW = 12;   // doubles per stored contribution
+__global__ void __launch_bounds__(256) k_explicit_contrib(DevProblem P) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.ex_ncontrib) return;
+    const int qa = __ldcs(P.ex_qa + c), qb = __ldcs(P.ex_qb + c);
+    const size_t dest = (size_t)__ldcs(P.ex_dest + c);
+    const int pt = __ldg(P.q_pt + qa);
+    const size_t Nq = (size_t)P.Nq;
+    double Aa[6], Ab[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) { Aa[i] = __ldg(P.qA + (size_t)i * Nq + qa); Ab[i] = __ldg(P.qA + (size_t)i * Nq + qb); }
+    const d4 X = ld256(P.pts + 4 * (size_t)pt);
+    const d4 h0 = ld256(P.Hinv + 8 * (size_t)pt), h1 = ld256(P.Hinv + 8 * (size_t)pt + 4);   // (h00 h01 h02 h11) (h12 h22 - -)
+    // E = Aa Hinv (2x3)
+    const double E0 = Aa[0] * h0.x + Aa[1] * h0.y + Aa[2] * h0.z, E1 = Aa[0] * h0.y + Aa[1] * h0.w + Aa[2] * h1.x,
+                 E2 = Aa[0] * h0.z + Aa[1] * h1.x + Aa[2] * h1.y;
+    const double E3 = Aa[3] * h0.x + Aa[4] * h0.y + Aa[5] * h0.z, E4 = Aa[3] * h0.y + Aa[4] * h0.w + Aa[5] * h1.x,
+                 E5 = Aa[3] * h0.z + Aa[4] * h1.x + Aa[5] * h1.y;
+    // G = E Ab^T (2x2)
+    const double G00 = E0 * Ab[0] + E1 * Ab[1] + E2 * Ab[2], G01 = E0 * Ab[3] + E1 * Ab[4] + E2 * Ab[5];
+    const double G10 = E3 * Ab[0] + E4 * Ab[1] + E5 * Ab[2], G11 = E3 * Ab[3] + E4 * Ab[4] + E5 * Ab[5];
+    // F = G Ab (2x3);  K = Aa^T F (3x3)
+    double F[6];
+#pragma unroll
+    for (int j = 0; j < 3; j++) { F[j] = G00 * Ab[j] + G01 * Ab[3 + j]; F[3 + j] = G10 * Ab[j] + G11 * Ab[3 + j]; }
+    double K[9];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) K[3 * r + j] = Aa[r] * F[j] + Aa[3 + r] * F[3 + j];
+    double* o = P.ex_contrib + EX_CW * dest;   // 96 B, 32-byte aligned
+    st256(o, K[0], K[1], K[2], K[3]);
+    st256(o + 4, K[4], K[5], K[6], K[7]);
+    st256(o + 8, K[8], X.x, X.y, X.z);
+}
+
+// ---------------------------------------------------------------------------
+// assembly: one THREAD per off-diagonal block (i < j).  The run of the block is contiguous in the buffer; the thread
+// streams it with 256-bit loads, expands every contribution with its block-constant camera centres and keeps the 36
+// sums in registers (run order -> deterministic, no shuffles).  Then S_ij = -T_i (sum B) T_j^T, T = diag(Q, I), is
+// written into its tile.  Blocks touching a fixed camera are zero (its Jc is zero in the reference's linearisation).
+// Neighbouring threads hold neighbouring j of the same i: similar run lengths, adjacent 48-byte row segments.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ size_t ex_elem(const DevProblem& P, int i, int j) {   // offset of element (0,0) of block (i,j), i <= j
+    const int I = i / EX_TB, J = j / EX_TB;
+    const int tile = P.ex_tile_of[I * P.ex_NT + J];
+    return (size_t)tile * EX_TD * EX_TD + (size_t)(6 * (i - I * EX_TB)) * EX_TD + 6 * (j - J * EX_TB);
+}
+__global__ void __launch_bounds__(128) k_explicit_assemble(DevProblem P) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= P.ex_nblocks) return;
+    const int i = __ldg(P.ex_blk_i + b), j = __ldg(P.ex_blk_j + b);
+    const int r0 = __ldg(P.ex_blk_off + b), r1 = r0 + __ldg(P.ex_blk_len + b);
+    const d4 ti = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * i + 8);   // (Rt8, t0, t1, t2)
+    const d4 tj = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * j + 8);
+    double B[36];
+#pragma unroll
+    for (int e = 0; e < 36; e++) B[e] = 0.0;
+    const double* src = P.ex_contrib + EX_CW * (size_t)r0;
+    d4 n0 = ld256(src), n1 = ld256(src + 4), n2 = ld256(src + 8);   // r1 > r0 always
+    for (int r = r0; r < r1; r++) {
+        const d4 k0 = n0, k1 = n1, k2 = n2;
+        src += EX_CW;
+        if (r + 1 < r1) { n0 = ld256(src); n1 = ld256(src + 4); n2 = ld256(src + 8); }   // next contribution in flight during the math
+        const double K[9] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w, k2.x};
+        const double da[3] = {k2.y - ti.y, k2.z - ti.z, k2.w - ti.w};
+        const double db[3] = {k2.y - tj.y, k2.z - tj.z, k2.w - tj.w};
+        // U = [da]x K : column c of U = da x K[:,c]
+        double U[9];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            U[c] = da[1] * K[6 + c] - da[2] * K[3 + c];
+            U[3 + c] = da[2] * K[c] - da[0] * K[6 + c];
+            U[6 + c] = da[0] * K[3 + c] - da[1] * K[c];
+        }
+        // M [db]x : row r = M[r,:] x db
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            const double u0 = U[3 * q], u1 = U[3 * q + 1], u2 = U[3 * q + 2];
+            B[6 * q + 0] -= u1 * db[2] - u2 * db[1]; B[6 * q + 1] -= u2 * db[0] - u0 * db[2]; B[6 * q + 2] -= u0 * db[1] - u1 * db[0];
+            B[6 * q + 3] += u0; B[6 * q + 4] += u1; B[6 * q + 5] += u2;
+            const double v0 = K[3 * q], v1 = K[3 * q + 1], v2 = K[3 * q + 2];
+            B[6 * (3 + q) + 0] -= v1 * db[2] - v2 * db[1]; B[6 * (3 + q) + 1] -= v2 * db[0] - v0 * db[2]; B[6 * (3 + q) + 2] -= v0 * db[1] - v1 * db[0];
+            B[6 * (3 + q) + 3] += v0; B[6 * (3 + q) + 4] += v1; B[6 * (3 + q) + 5] += v2;
+        }
+    }
+    double* out = P.ex_S + ex_elem(P, i, j);
+    if (P.cam_fixed[i] || P.cam_fixed[j]) {
+#pragma unroll
+        for (int r = 0; r < 6; r++)
+#pragma unroll
+            for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, 0.0, 0.0);
+        return;
+    }
+    // S_ij = -T_i B T_j^T, T = diag(Q, I): first the left factor on the top three rows, then the right factor on the left
+    // three columns
+    double Qm[9];
+    {
+        const double* Qi = P.cam_Q + 12 * (size_t)i;
+        const d4 q0 = ld256(Qi), q1 = ld256(Qi + 4), q2 = ld256(Qi + 8);
+        Qm[0] = q0.x; Qm[1] = q0.y; Qm[2] = q0.z; Qm[3] = q0.w; Qm[4] = q1.x; Qm[5] = q1.y; Qm[6] = q1.z; Qm[7] = q1.w; Qm[8] = q2.x;
+    }
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+        const double b0 = B[c], b1 = B[6 + c], b2 = B[12 + c];
+        B[c] = Qm[0] * b0 + Qm[1] * b1 + Qm[2] * b2;
+        B[6 + c] = Qm[3] * b0 + Qm[4] * b1 + Qm[5] * b2;
+        B[12 + c] = Qm[6] * b0 + Qm[7] * b1 + Qm[8] * b2;
+    }
+    {
+        const double* Qj = P.cam_Q + 12 * (size_t)j;
+        const d4 q0 = ld256(Qj), q1 = ld256(Qj + 4), q2 = ld256(Qj + 8);
+        Qm[0] = q0.x; Qm[1] = q0.y; Qm[2] = q0.z; Qm[3] = q0.w; Qm[4] = q1.x; Qm[5] = q1.y; Qm[6] = q1.z; Qm[7] = q1.w; Qm[8] = q2.x;
+    }
+#pragma unroll
+    for (int r = 0; r < 6; r++) {
+        const double b0 = B[6 * r], b1 = B[6 * r + 1], b2 = B[6 * r + 2];
+        // (B Tj^T)[r][c] = sum_b B[r][b] Qj[c][b]
+        B[6 * r] = b0 * Qm[0] + b1 * Qm[1] + b2 * Qm[2];
+        B[6 * r + 1] = b0 * Qm[3] + b1 * Qm[4] + b2 * Qm[5];
+        B[6 * r + 2] = b0 * Qm[6] + b1 * Qm[7] + b2 * Qm[8];
+    }
+#pragma unroll
+    for (int r = 0; r < 6; r++)
+#pragma unroll
+        for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, -B[6 * r + c], -B[6 * r + c + 1]);
+}
+
+// diagonal blocks: S_ii = Hcc + lam - Sd, stored HALVED in the diagonal tiles (T x + T^T x counts them twice)
+__global__ void k_explicit_diag(DevProblem P) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= P.Nc * 36) return;
+    const int c = t / 36, e = t - 36 * c, r = e / 6, cc = e - 6 * r;
+    const int q = sym6(r, cc);
+    double v = P.Hcc[21 * (size_t)c + q] - P.Sd[21 * (size_t)c + q];
+    if (r == cc) v += P.lam_c[6 * (size_t)c + r];
+    P.ex_S[ex_elem(P, c, c) + (size_t)r * EX_TD + cc] = 0.5 * v;
+}
+
+void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
+    if (!P.ex_on) return;
+    if (P.ex_ncontrib) k_explicit_contrib<<<cdiv(P.ex_ncontrib, 256), 256, 0, st>>>(P);
+    if (P.ex_nblocks) k_explicit_assemble<<<cdiv(P.ex_nblocks, 128), 128, 0, st>>>(P);
+    k_explicit_diag<<<cdiv(P.Nc * 36, 256), 256, 0, st>>>(P);
+}
+
+// ---------------------------------------------------------------------------
+// mat-vec on the tiles.  CTA = (tile, 64-row chunk), 4 warps x 16 rows.  Lane l owns the columns l + 32 k
+// (k < 12) of the tile: every load instruction of a warp is one coalesced 256-byte run of a tile row, read once
+// and used for BOTH products
+//   row partial  y_I[r] += sum_c T[r][c] x_J[c]   (8 rows at a time in registers, then ONE split butterfly:
+//                                                  9 double shuffles for the 8 sums instead of 40)
+//   col partial  y_J[c] += sum_r T[r][c] x_I[r]   (12 register accumulators per lane, no shuffles at all;
+//                                                  the four warps are folded through shared memory in warp order).
+// Algorithmic bytes: 8 B per stored scalar, i.e. 384*384*8 per tile -- the whole symmetric product from one read.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    double r[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = (b4 ? v[4 + i] : v[i]) + __shfl_xor_sync(FULL, b4 ? v[i] : v[4 + i], 16);
+    double p[2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) p[i] = (b3 ? r[2 + i] : r[i]) + __shfl_xor_sync(FULL, b3 ? r[i] : r[2 + i], 8);
+    double q = (b2 ? p[1] : p[0]) + __shfl_xor_sync(FULL, b2 ? p[0] : p[1], 4);
+    q += __shfl_xor_sync(FULL, q, 2);
+    q += __shfl_xor_sync(FULL, q, 1);
+    return q;   // total of value (lane >> 2) in every lane
+}
+__global__ void __launch_bounds__(128) k_explicit_matvec(DevProblem P, const double* __restrict__ x) {
+    __shared__ double s_col[4][EX_TD];
+    const int tile = blockIdx.x / EX_NCHUNK, h = blockIdx.x - tile * EX_NCHUNK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int I = __ldg(P.ex_tile_I + tile), J = __ldg(P.ex_tile_J + tile);
+    const int n = 6 * P.Nc;
+    const double* T = P.ex_S + (size_t)tile * EX_TD * EX_TD;
+    double xJ[12], col[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+        const int g = EX_TD * J + lane + 32 * k;
+        xJ[k] = g < n ? __ldg(x + g) : 0.0;
+        col[k] = 0.0;
+    }
+    const int row0 = EX_CHUNK * h + 16 * warp;
+#pragma unroll 1
+    for (int g8 = 0; g8 < 2; g8++) {
+        double racc[8];
+#pragma unroll
+        for (int rr = 0; rr < 8; rr++) {
+            const int r = row0 + 8 * g8 + rr;
+            const int gi = EX_TD * I + r;
+            const double xi = gi < n ? __ldg(x + gi) : 0.0;   // warp-uniform
+            const double* Tr = T + (size_t)r * EX_TD + lane;
+            double acc = 0.0;
+#pragma unroll
+            for (int k = 0; k < 12; k++) {
+                const double v = __ldcs(Tr + 32 * k);
+                acc += v * xJ[k];
+                col[k] += v * xi;
+            }
+            racc[rr] = acc;
+        }
+        const double s = warp_sum8(racc, lane);
+        if ((lane & 3) == 0) P.ex_row[(size_t)tile * EX_TD + row0 + 8 * g8 + (lane >> 2)] = s;
+    }
+#pragma unroll
+    for (int k = 0; k < 12; k++) s_col[warp][lane + 32 * k] = col[k];
+    __syncthreads();
+    for (int c = threadIdx.x; c < EX_TD; c += 128)
+        P.ex_col[((size_t)tile * EX_NCHUNK + h) * EX_TD + c] = ((s_col[0][c] + s_col[1][c]) + s_col[2][c]) + s_col[3][c];
+}
+void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st) {
+    if (P.ex_ntiles) k_explicit_matvec<<<P.ex_ntiles * EX_NCHUNK, 128, 0, st>>>(P, x);
+}
+
+__global__ void __launch_bounds__(128) k_explicit_gather(DevProblem P, double* y) {
+    __shared__ int s_off[128];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < 6 * P.Nc;
+    const double v = explicit_fold(P, i, valid, s_off);
+    if (valid) y[i] = v;
+}
+void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st) {
+    k_explicit_gather<<<cdiv(6 * P.Nc, 128), 128, 0, st>>>(P, y);
+}
+
+}  // namespace sba

@@ -68,16 +68,21 @@ __device__ __forceinline__ bool pcg_frozen(const DevProblem& P, double tol2, int
     return !(rz > tol2 * rz0) || !(rz0 > 0.0) || P.flags[FL_PCG_ITERS] >= max_iters;
 }
 
-// mode 0: q = -sum tiles + Hcc p + lam p (single GPU);  mode 1: q (all-reduced partial) += Hcc p + lam p
+// mode 0: q = -sum tiles + Hcc p + lam p (single GPU);  mode 1: q (all-reduced partial) += Hcc p + lam p;
+// mode 2: q = S p folded from the tile partials of the explicit system (Hcc, lam and the Schur term are all inside S)
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_A(DevProblem P, int mode) {
     __shared__ double sh[33];
+    __shared__ int s_off[PCG_BLOCK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
+    double folded = 0.0;
+    if (mode == 2) folded = explicit_fold(P, i, i < n, s_off);   // block-uniform branch (barriers inside)
     if (i == 0) { P.scalars[SC_RZ] = P.scalars[SC_RZ_NEXT]; P.flags[FL_PCG_ITERS] = P.flags[FL_PCG_ITERS_NEXT]; }
     double pq = 0.0;
     if (i < n) {
         const int c = i / 6, a = i - 6 * c;
         double acc = 0.0;
-        if (mode == 0) {
+        if (mode == 2) {
+        } else if (mode == 0) {
             if (!P.cam_fixed[c]) {
                 acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
             }
@@ -85,12 +90,16 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_A(DevProblem P, int mode) {
         } else {
             acc = P.pcg_q[i];
         }
-        const double* H = P.Hcc + 21 * (size_t)c;
         const double* p = P.pcg_p + 6 * (size_t)c;
-        double hx = 0.0;
+        if (mode == 2) {
+            acc = folded;
+        } else {
+            const double* H = P.Hcc + 21 * (size_t)c;
+            double hx = 0.0;
 #pragma unroll
-        for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
-        acc += hx + P.lam_c[i] * p[a];
+            for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
+            acc += hx + P.lam_c[i] * p[a];
+        }
         P.pcg_q[i] = acc;
         pq = p[a] * acc;
     }
@@ -148,7 +157,10 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
     cg::grid_group grid = cg::this_grid();
     __shared__ double sh[33];
     __shared__ double sr[PCG_BLOCK];
+    __shared__ int s_off[PCG_BLOCK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
+    double folded = 0.0;
+    if (mode == 2) folded = explicit_fold(P, i, i < n, s_off);   // block-uniform branch (barriers inside)
     // ---- A (reads the scalars of the previous iteration through the NEXT copies: nobody writes them before the last barrier)
     const double rz = P.scalars[SC_RZ_NEXT], rz0 = P.scalars[SC_RZ0];
     const int it = P.flags[FL_PCG_ITERS_NEXT];
@@ -157,7 +169,8 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
     if (i < n) {
         const int c = i / 6, a = i - 6 * c;
         double acc = 0.0;
-        if (mode == 0) {
+        if (mode == 2) {
+        } else if (mode == 0) {
             if (!P.cam_fixed[c]) {
                 acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
             }
@@ -165,13 +178,17 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
         } else {
             acc = P.pcg_q[i];
         }
-        const double* H = P.Hcc + 21 * (size_t)c;
         const double* p = P.pcg_p + 6 * (size_t)c;
-        double hx = 0.0;
-#pragma unroll
-        for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
         p_i = p[a];
-        q_i = acc + (hx + P.lam_c[i] * p_i);
+        if (mode == 2) {
+            q_i = folded;
+        } else {
+            const double* H = P.Hcc + 21 * (size_t)c;
+            double hx = 0.0;
+#pragma unroll
+            for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
+            q_i = acc + (hx + P.lam_c[i] * p_i);
+        }
         P.pcg_q[i] = q_i;
         pq = p_i * q_i;
     }

@@ -101,6 +101,8 @@ private:
     int build_rhs_and_preconditioner(bool* ok);            // damped inverse, reduced rhs, Minv
     int schur_apply(const double* x, double* y);           // y = S x  (x zero at fixed cameras)
     int run_pcg(int* iters);
+    int build_explicit_structure(const std::vector<int32_t>& pt_cnt, const std::vector<int32_t>& pt_q0,
+                                 const std::vector<int32_t>& q_cam);   // sba_solver_explicit.inc
 
     // host copies (caller order)
     double* h_raxis = nullptr; double* h_t = nullptr; double* h_xyz = nullptr;   // caller-owned

@@ -115,9 +115,10 @@ def test_normal_blocks(oracle, kw):
 
 
 @pytest.mark.parametrize("kw", [dict(), dict(spherical=True), dict(mixed=True)])
-@pytest.mark.parametrize("operator_mode", [0, 1])
+@pytest.mark.parametrize("operator_mode", [0, 1, 2, 3])
 def test_schur_matvec_and_rhs(oracle, kw, operator_mode):
-    """operator_mode 0 = factored camera pass (A, C rebuilt from Pbar), 1 = materialised A, C."""
+    """operator_mode 0 = auto, 1 = implicit with materialised A, C, 2 = implicit with the factored camera pass
+    (A, C rebuilt from Pbar), 3 = explicit reduced camera system (dense tiles, static contribution slots)."""
     sc = synthetic.make_scene("small", **kw)
     rng = np.random.default_rng(9)
     lam_c = rng.uniform(0.5, 2.0, (sc["n_cams"], 6)); lam_p = rng.uniform(0.5, 2.0, (sc["n_pts"], 3))
@@ -131,9 +132,27 @@ def test_schur_matvec_and_rhs(oracle, kw, operator_mode):
 
 def test_operator_modes_agree_on_lm():
     sc = synthetic.make_scene("ladybug", mixed=True)
-    a = gpu_solver(sc, operator_mode=0)[0].solve(max_iterations=4, **FIXED_ITERS)
     b = gpu_solver(sc, operator_mode=1)[0].solve(max_iterations=4, **FIXED_ITERS)
-    assert abs(a["final_cost"] - b["final_cost"]) <= 1e-10 * b["final_cost"]
+    for mode in (0, 2, 3):
+        a = gpu_solver(sc, operator_mode=mode)[0].solve(max_iterations=4, **FIXED_ITERS)
+        assert abs(a["final_cost"] - b["final_cost"]) <= 1e-10 * b["final_cost"], mode
+        for ca, cb in zip(a["cost_history"], b["cost_history"]):
+            assert abs(ca - cb) <= 1e-9 * cb, mode
+
+
+def test_explicit_system_with_fixed_cameras_and_heavy_points(oracle):
+    """Explicit tiles: a fixed camera in the middle, a point seen by more than 32 cameras, more than one tile per side."""
+    sc = synthetic.make_scene(None, n_cams=150, n_pts=600, n_obs=6000, seed=5, window=60)
+    sc["cam_fixed"] = sc["cam_fixed"].copy(); sc["cam_fixed"][77] = 1
+    rng = np.random.default_rng(3)
+    lam_c = rng.uniform(0.5, 2.0, (sc["n_cams"], 6)); lam_p = rng.uniform(0.5, 2.0, (sc["n_pts"], 3))
+    x = rng.normal(size=(sc["n_cams"], 6))
+    yo, ro = oracle.Problem(sc).schur_matvec(lam_c, lam_p, x)
+    for mode in (2, 3):
+        s, _ = gpu_solver(sc, operator_mode=mode)
+        y, r = s.schur_matvec(lam_c, lam_p, x)
+        assert relerr(y, yo) < 1e-11, mode
+        assert relerr(r, ro) < 1e-11, mode
 
 
 @pytest.mark.parametrize("name", ["small_scene", "small_scene_spherical", "small_scene_mixed", "ladybug_scene"])
