@@ -149,7 +149,7 @@ def bench_config(a):
     return {"workload": f"synthetic {a.shape}-shape BA: {nc} cameras / {npt} points / {no} observations, plane cost, "
                         "intrinsics constant, first camera fixed, 4 GCP priors",
             "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
-            "linear_solver": "implicit Schur complement + SCHUR_JACOBI PCG",
+            "linear_solver": "Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric tiles, rebuilt every LM iteration) on 1 GPU, implicit operator when sharded",
             "step": "one LM iteration, fixed count (tolerances 0), every run restarts from the same initial values",
             "l2": "working set ~1.2 GB per evaluation >> 126 MB L2 (no flush needed)",
             "parallelism": f"points sharded over {a.gpus} GPU(s), cameras replicated"}
@@ -164,6 +164,7 @@ ALG_BYTES = {
                                      # from L1/L2; ~26 B/obs of Hinv / y_p per point not counted)
 }
 STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6}
+TILE_BYTES = 384 * 384 * 8           # one dense tile of the explicit reduced camera system
 
 
 def run_b200(a):
@@ -264,9 +265,24 @@ def run_b200(a):
     kern = {}
     for name, stage in STAGE.items():
         ms = s.time_stage(stage, 20)
-        kern[name] = {"ms": ms, "GBps": ALG_BYTES[name] * n_obs_local / (ms * 1e-3) / 1e9, "Mobs_per_s": n_obs_local / ms / 1e3}
+        kern[name] = {"ms": ms, "GBps": ALG_BYTES[name] * n_obs_local / (ms * 1e-3) / 1e9, "Mobs_per_s": n_obs_local / ms / 1e3,
+                      "alg_bytes_per_launch": ALG_BYTES[name] * n_obs_local, "alg_bytes_per_obs": ALG_BYTES[name]}
     pcg_per_step = r["pcg_iterations_total"] / max(r["iterations"], 1)
-    share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
+    ex = s.explicit_info()
+    if ex["enabled"]:
+        # the PCG applies S from the dense tiles: ONE read of every stored scalar per application (symmetric storage)
+        ms = s.time_stage(10, 20)
+        nbytes = ex["n_tiles"] * TILE_BYTES
+        kern["k_explicit_matvec"] = {"ms": ms, "GBps": nbytes / (ms * 1e-3) / 1e9, "alg_bytes_per_launch": nbytes,
+                                     "alg_bytes_per_tile": TILE_BYTES, "tiles": ex["n_tiles"]}
+        ms = s.time_stage(11, 10)
+        nbytes = ex["n_contributions"] * (12 + 2 * 96) + ex["n_blocks"] * (288 + 16)   # index + write + read of the compact contributions, block out
+        kern["explicit_build"] = {"ms": ms, "GBps": nbytes / (ms * 1e-3) / 1e9, "alg_bytes_per_launch": nbytes,
+                                  "contributions": ex["n_contributions"], "blocks": ex["n_blocks"]}
+        share = {"k_explicit_matvec": pcg_per_step * kern["k_explicit_matvec"]["ms"], "explicit_build": kern["explicit_build"]["ms"],
+                 "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
+    else:
+        share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
     dom = max(share, key=share.get)
     traffic = None
     try:
@@ -275,10 +291,9 @@ def run_b200(a):
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
                 "frac": kern[dom]["GBps"] / peak, "traffic": traffic, "peak_source": peak_kind,
-                "alg_bytes_per_obs": ALG_BYTES[dom], "obs_per_launch": n_obs_local,
+                "alg_bytes_per_launch": kern[dom]["alg_bytes_per_launch"], "obs_per_launch": n_obs_local,
                 "share_of_step": share[dom] / (ms_total / a.steps),
-                "kernels": {k: {"ms": v["ms"], "GBps": v["GBps"], "frac": v["GBps"] / peak, "alg_bytes_per_obs": ALG_BYTES[k]}
-                            for k, v in kern.items()}}
+                "kernels": {k: dict(v, frac=v["GBps"] / peak) for k, v in kern.items()}}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:

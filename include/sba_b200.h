@@ -194,8 +194,10 @@ int sba_set_options(sba_solver* s, const sba_options* o);
 /* Kernel-level timing hook for bench.py: runs `reps` back-to-back launches of
  * one pipeline stage on the resident problem and returns the mean device time
  * per launch in ms (CUDA events on the solver's stream).
- * stage: 0 = K1 residual+Jacobian, 1 = K1c cost only, 2 = K2 Schur assembly
- * (point blocks + camera blocks), 3 = implicit Schur mat-vec, 4 = preconditioner build. */
+ * stage: 0 = K1 residual+Jacobian, 1 = K1c cost only, 2 = K1p/K2a (fused) + K2b, 3 = reduced-system mat-vec (the
+ * operator the PCG applies: explicit tiles or implicit passes), 4 = preconditioner build, 5 = K1p/K2a, 6 = implicit
+ * point pass, 7 = implicit camera pass, 9 = K2b camera blocks, 10 = explicit tile mat-vec kernel, 11 = explicit build
+ * (contributions + assembly + diagonal). */
 int sba_time_stage(sba_solver* s, int32_t stage, int32_t reps, double* ms_per_launch);
 
 /* Batched multi-view DLT triangulation (adjacent to the LM loop; reference has
@@ -223,6 +225,13 @@ int sba_partition_points(int32_t n_pts, const int32_t* obs_per_point,
  * camera-sorted slot count, n_tiles the warp tiles */
 int sba_problem_sizes(const sba_solver* s, int32_t* n_cams, int32_t* n_pts,
                       int32_t* n_obs, int32_t* n_slots, int32_t* n_tiles);
+
+/* explicit reduced camera system (operator_mode 0 auto / 3): whether the PCG applies S from the dense 384x384 tiles,
+ * and the static sizes of that structure (tiles over the upper block triangle, off-diagonal 6x6 blocks with a common
+ * point, point-pair contributions).  Replaces nothing in the reference: Ceres keeps the same numbers private in its
+ * SchurEliminator / BlockRandomAccessSparseMatrix (behind modularsbasolver.cpp:938); exposed for measurement. */
+int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles,
+                      int32_t* n_blocks, int32_t* n_contributions);
 
 const char* sba_version(void);
 

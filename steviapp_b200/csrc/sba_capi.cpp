@@ -114,4 +114,12 @@ int sba_problem_sizes(const sba_solver* s, int32_t* n_cams, int32_t* n_pts, int3
     return SBA_OK;
 }
 
+int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles, int32_t* n_blocks, int32_t* n_contributions) {
+    GUARD(s);
+    const sba::DevProblem& P = s->impl.P;
+    if (enabled) *enabled = P.ex_on; if (n_tiles) *n_tiles = P.ex_ntiles;
+    if (n_blocks) *n_blocks = P.ex_nblocks; if (n_contributions) *n_contributions = P.ex_ncontrib;
+    return SBA_OK;
+}
+
 }  // extern "C"

@@ -186,6 +186,12 @@ class SBASolver:
         self._check(self._lib.sba_problem_sizes(self._h, *[C.byref(x) for x in v]))
         return dict(zip(("n_cams", "n_pts", "n_obs", "n_slots", "n_tiles"), [x.value for x in v]))
 
+    def explicit_info(self):
+        """Static sizes of the explicit reduced camera system (enabled = the PCG applies S from the tiles)."""
+        v = [C.c_int32() for _ in range(4)]
+        self._check(self._lib.sba_explicit_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("enabled", "n_tiles", "n_blocks", "n_contributions"), [x.value for x in v]))
+
     # -- evaluation hooks -------------------------------------------------
     def upload_parameters(self):
         self._check(self._lib.sba_upload_parameters(self._h))
