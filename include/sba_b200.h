@@ -233,6 +233,12 @@ int sba_problem_sizes(const sba_solver* s, int32_t* n_cams, int32_t* n_pts,
 int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles,
                       int32_t* n_blocks, int32_t* n_contributions);
 
+/* inspection hook: copies the tiles of the explicit reduced camera system as last built (n_tiles * 384 * 384 doubles,
+ * row-major tiles; tile t covers camera tiles (tile_i[t], tile_j[t]), i <= j; diagonal tiles hold S_ii / 2 on their
+ * block diagonal and zeros below) and the reduced right-hand side (6 * n_cams).  Any pointer may be NULL.  The analogue
+ * in the reference is reading Ceres' reduced system, which Ceres does not expose; used by tests and scripts only. */
+int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* tile_j, double* rhs);
+
 const char* sba_version(void);
 
 #ifdef __cplusplus

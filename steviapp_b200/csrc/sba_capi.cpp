@@ -122,4 +122,17 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles, i
     return SBA_OK;
 }
 
+int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* tile_j, double* rhs) {
+    GUARD(s);
+    const sba::DevProblem& P = s->impl.P;
+    if (!P.ex_on) return SBA_ERR_INVALID;
+    cudaDeviceSynchronize();
+    const size_t n = (size_t)P.ex_ntiles;
+    if (tiles && cudaMemcpy(tiles, P.ex_S, n * 384 * 384 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
+    if (tile_i && cudaMemcpy(tile_i, P.ex_tile_I, n * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
+    if (tile_j && cudaMemcpy(tile_j, P.ex_tile_J, n * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
+    if (rhs && cudaMemcpy(rhs, P.rhs, 6 * (size_t)P.Nc * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
+    return SBA_OK;
+}
+
 }  // extern "C"

@@ -184,7 +184,8 @@ void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
 // explicit reduced camera system
 void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> tiles (needs Hinv, Sd, lam_c of this LM iteration)
-void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st);   // tile partials ex_row / ex_col of S x
+void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg = 0, double tol2 = 0.0,
+                            int max_iters = 0);   // tile partials ex_row / ex_col of S x (pcg: skip once the PCG is frozen)
 void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);

@@ -133,7 +133,8 @@ __device__ __forceinline__ void cam_vec_store(const DevProblem& P, int c, const 
 // ---- explicit reduced camera system (sba_kernels_explicit.cu): tile geometry and the fold of the mat-vec partials
 constexpr int EX_TB = 64;            // cameras per tile side
 constexpr int EX_TD = 6 * EX_TB;     // 384 scalars per tile side
-constexpr int EX_CHUNK = 64;         // rows per mat-vec CTA
+constexpr int EX_CHUNK = 64;         // rows per mat-vec CTA (128 measured slower: 0.093 vs 0.085 ms) (EXH_NCHUNK in sba_solver_explicit.inc = EX_TD / EX_CHUNK)
+constexpr int EX_MVW = EX_CHUNK / 16; // warps per mat-vec CTA, 16 rows each
 constexpr int EX_NCHUNK = EX_TD / EX_CHUNK;
 
 // y = S x from the partials, element i of camera tile K: the static list ex_fold_off[ex_fold_ptr[K] .. ex_fold_ptr[K+1])

@@ -175,7 +175,7 @@ void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------
-// mat-vec on the tiles.  CTA = (tile, 64-row chunk), 4 warps x 16 rows.  Lane l owns the columns l + 32 k
+// mat-vec on the tiles.  CTA = (tile, EX_CHUNK-row chunk), EX_MVW warps x 16 rows.  Lane l owns the columns l + 32 k
 // (k < 12) of the tile: every load instruction of a warp is one coalesced 256-byte run of a tile row, read once
 // and used for BOTH products
 //   row partial  y_I[r] += sum_c T[r][c] x_J[c]   (8 rows at a time in registers, then ONE split butterfly:
@@ -197,8 +197,14 @@ __device__ __forceinline__ double warp_sum8(const double (&v)[8], int lane) {
     q += __shfl_xor_sync(FULL, q, 1);
     return q;   // total of value (lane >> 2) in every lane
 }
-__global__ void __launch_bounds__(128) k_explicit_matvec(DevProblem P, const double* __restrict__ x) {
-    __shared__ double s_col[4][EX_TD];
+// pcg != 0: launched inside the PCG batch -- return at once when the solve has already converged / hit its cap (the
+// host reads the convergence scalar only every pcg_check_every iterations; same freeze rule as k_pcg_ABC)
+__global__ void __launch_bounds__(32 * EX_MVW) k_explicit_matvec(DevProblem P, const double* __restrict__ x, int pcg, double tol2, int max_iters) {
+    __shared__ double s_col[EX_MVW][EX_TD];
+    if (pcg) {
+        const double rz = P.scalars[SC_RZ_NEXT], rz0 = P.scalars[SC_RZ0];
+        if (!(rz > tol2 * rz0) || !(rz0 > 0.0) || P.flags[FL_PCG_ITERS_NEXT] >= max_iters) return;   // uniform over the grid
+    }
     const int tile = blockIdx.x / EX_NCHUNK, h = blockIdx.x - tile * EX_NCHUNK;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int I = __ldg(P.ex_tile_I + tile), J = __ldg(P.ex_tile_J + tile);
@@ -236,11 +242,15 @@ __global__ void __launch_bounds__(128) k_explicit_matvec(DevProblem P, const dou
 #pragma unroll
     for (int k = 0; k < 12; k++) s_col[warp][lane + 32 * k] = col[k];
     __syncthreads();
-    for (int c = threadIdx.x; c < EX_TD; c += 128)
-        P.ex_col[((size_t)tile * EX_NCHUNK + h) * EX_TD + c] = ((s_col[0][c] + s_col[1][c]) + s_col[2][c]) + s_col[3][c];
+    for (int c = threadIdx.x; c < EX_TD; c += 32 * EX_MVW) {
+        double a = s_col[0][c];
+#pragma unroll
+        for (int w = 1; w < EX_MVW; w++) a += s_col[w][c];   // warp order: fixed
+        P.ex_col[((size_t)tile * EX_NCHUNK + h) * EX_TD + c] = a;
+    }
 }
-void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st) {
-    if (P.ex_ntiles) k_explicit_matvec<<<P.ex_ntiles * EX_NCHUNK, 128, 0, st>>>(P, x);
+void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg, double tol2, int max_iters) {
+    if (P.ex_ntiles) k_explicit_matvec<<<P.ex_ntiles * EX_NCHUNK, 32 * EX_MVW, 0, st>>>(P, x, pcg, tol2, max_iters);
 }
 
 __global__ void __launch_bounds__(128) k_explicit_gather(DevProblem P, double* y) {

@@ -192,6 +192,23 @@ class SBASolver:
         self._check(self._lib.sba_explicit_info(self._h, *[C.byref(x) for x in v]))
         return dict(zip(("enabled", "n_tiles", "n_blocks", "n_contributions"), [x.value for x in v]))
 
+    def explicit_dense(self):
+        """The reduced camera system of the last LM iteration as a dense symmetric matrix (6 n_cams)^2 and its rhs
+        (inspection hook over sba_explicit_tiles; small problems / studies only)."""
+        info = self.explicit_info()
+        if not info["enabled"]:
+            raise SBAError(-1, "explicit reduced camera system is off")
+        nt, nc = info["n_tiles"], self.sizes()["n_cams"]
+        tiles = np.empty((nt, 384, 384)); ti = np.empty(nt, dtype=np.int32); tj = np.empty(nt, dtype=np.int32)
+        rhs = np.empty(6 * nc)
+        self._check(self._lib.sba_explicit_tiles(self._h, _ptr(tiles), _ptr(ti), _ptr(tj), _ptr(rhs)))
+        NT = (nc + 63) // 64
+        U = np.zeros((NT * 384, NT * 384))
+        for t in range(nt):
+            U[384 * ti[t]:384 * ti[t] + 384, 384 * tj[t]:384 * tj[t] + 384] = tiles[t]
+        S = U + U.T          # diagonal tiles store S_ii / 2 and nothing below: the sum restores the symmetric matrix
+        return S[:6 * nc, :6 * nc], rhs
+
     # -- evaluation hooks -------------------------------------------------
     def upload_parameters(self):
         self._check(self._lib.sba_upload_parameters(self._h))
