@@ -1,5 +1,8 @@
-"""Multi-GPU parity check, run under torchrun: sharded solve (NCCL) vs the same problem on one GPU.
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 scripts/multigpu_check.py [shape] [iters]"""
+"""Multi-GPU parity check, run under torchrun: sharded solve vs the same problem on one GPU, for every way the sharded
+PCG can apply the reduced camera system:
+  explicit tiles (reduce-scattered) or implicit operator  x  all-reduce over peer mailboxes (fused kernel) or NCCL.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+      scripts/multigpu_check.py [shape] [iters]"""
 import json
 import os
 import sys
@@ -18,31 +21,49 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 fixed = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
 sc = synthetic.make_scene(shape)
 sh = synthetic.shard_scene(sc, rank, world)
-s = SBASolver(device=local, pcg_check_every=4, **fixed)
-uid = [comm_unique_id() if rank == 0 else None]
-dist.broadcast_object_list(uid, src=0)
-s.comm_init(rank, world, uid[0])
-raxis, t, pts = synthetic.load_into(s, sh)
-r = s.solve(max_iterations=iters)
-out = {"rank": rank, "shard_obs": sh["n_obs"], "cost_history": r["cost_history"], "pcg": r["pcg_iters_history"], "ms_total": r["ms_total"]}
-gathered = [None] * world
-dist.all_gather_object(gathered, out)
-# camera blocks must be bit-identical on every rank (replicated state)
-cams = torch.from_numpy(np.concatenate([raxis.ravel(), t.ravel()])).cuda()
-ref = cams.clone()
-dist.broadcast(ref, src=0)
-same = bool(torch.equal(cams, ref))
-flags = [None] * world
-dist.all_gather_object(flags, same)
+
+r1 = None
 if rank == 0:
     s1 = SBASolver(device=local, pcg_check_every=4, **fixed)
     synthetic.load_into(s1, sc)
     r1 = s1.solve(max_iterations=iters)
-    rel = max(abs(a - b) / max(b, 1.0) for a, b in zip(r["cost_history"], r1["cost_history"]))
-    ok = rel < 1e-8 and all(flags) and all(g["cost_history"] == r["cost_history"] for g in gathered)
-    print(json.dumps({"shape": shape, "world": world, "ok": ok, "max_rel_cost_diff_vs_1gpu": rel, "replicated_cameras_bitwise_equal": flags,
-                      "cost_sharded": r["cost_history"], "cost_1gpu": r1["cost_history"], "pcg_sharded": r["pcg_iters_history"],
-                      "pcg_1gpu": r1["pcg_iters_history"], "ms_sharded": [g["ms_total"] for g in gathered], "ms_1gpu": r1["ms_total"],
-                      "shard_obs": [g["shard_obs"] for g in gathered]}))
-    assert ok
+    s1.close()
+
+results = []
+all_ok = True
+for name, op_mode, peer in (("explicit+peer", 3, "1"), ("explicit+nccl", 3, "0"), ("implicit+peer", 2, "1"), ("implicit+nccl", 2, "0")):
+    os.environ["SBA_PEER_XCHG"] = peer
+    s = SBASolver(device=local, pcg_check_every=4, operator_mode=op_mode, **fixed)
+    uid = [comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    s.comm_init(rank, world, uid[0])
+    raxis, t, pts = synthetic.load_into(s, sh)
+    s.finalize()
+    info = dict(s.explicit_info(), **s.explicit_shard())
+    r = s.solve(max_iterations=iters)
+    ra = (raxis.copy(), t.copy(), pts.copy())
+    out = {"rank": rank, "shard_obs": sh["n_obs"], "cost_history": r["cost_history"], "pcg": r["pcg_iters_history"],
+           "ms_total": r["ms_total"], "ms_pcg": r["ms_pcg"], "info": info}
+    gathered = [None] * world
+    dist.all_gather_object(gathered, out)
+    # camera blocks must be bit-identical on every rank (replicated state)
+    cams = torch.from_numpy(np.concatenate([ra[0].ravel(), ra[1].ravel()])).cuda()
+    ref = cams.clone()
+    dist.broadcast(ref, src=0)
+    same = bool(torch.equal(cams, ref))
+    flags = [None] * world
+    dist.all_gather_object(flags, same)
+    s.close()
+    if rank == 0:
+        rel = max(abs(a - b) / max(b, 1.0) for a, b in zip(r["cost_history"], r1["cost_history"]))
+        ok = rel < 1e-8 and all(flags) and all(g["cost_history"] == r["cost_history"] for g in gathered)
+        all_ok = all_ok and ok
+        results.append({"mode": name, "ok": ok, "max_rel_cost_diff_vs_1gpu": rel, "replicated_cameras_bitwise_equal": flags,
+                        "cost_sharded": r["cost_history"], "pcg_sharded": r["pcg_iters_history"],
+                        "ms_sharded": [g["ms_total"] for g in gathered], "ms_pcg": [g["ms_pcg"] for g in gathered],
+                        "info": [g["info"] for g in gathered], "shard_obs": [g["shard_obs"] for g in gathered]})
+if rank == 0:
+    print(json.dumps({"shape": shape, "world": world, "ok": all_ok, "cost_1gpu": r1["cost_history"], "pcg_1gpu": r1["pcg_iters_history"],
+                      "ms_1gpu": r1["ms_total"], "ms_pcg_1gpu": r1["ms_pcg"], "modes": results}))
+    assert all_ok
 dist.destroy_process_group()

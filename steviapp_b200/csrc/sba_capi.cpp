@@ -122,10 +122,18 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles, i
     return SBA_OK;
 }
 
+int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange) {
+    GUARD(s);
+    const sba::DevProblem& P = s->impl.P;
+    if (first_tile) *first_tile = P.ex_on ? P.ex_own0 : 0; if (n_own) *n_own = P.ex_on ? P.ex_nown : 0;
+    if (peer_exchange) *peer_exchange = P.xchg_n > 0 ? 1 : 0;
+    return SBA_OK;
+}
+
 int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* tile_j, double* rhs) {
     GUARD(s);
     const sba::DevProblem& P = s->impl.P;
-    if (!P.ex_on) return SBA_ERR_INVALID;
+    if (!P.ex_on || P.ex_Sown != P.ex_S) return SBA_ERR_INVALID;   // single-GPU inspection hook (a rank holds only its slice)
     cudaDeviceSynchronize();
     const size_t n = (size_t)P.ex_ntiles;
     if (tiles && cudaMemcpy(tiles, P.ex_S, n * 384 * 384 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;

@@ -15,6 +15,8 @@ struct NcclId { char internal[128]; };
 typedef int (*fn_get_id)(NcclId*);
 typedef int (*fn_init_rank)(void**, int, NcclId, int);
 typedef int (*fn_allreduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_allgather)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*fn_reducescatter)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef int (*fn_destroy)(void*);
 typedef const char* (*fn_errstr)(int);
 
@@ -23,6 +25,8 @@ struct Api {
     fn_get_id get_id = nullptr;
     fn_init_rank init_rank = nullptr;
     fn_allreduce allreduce = nullptr;
+    fn_allgather allgather = nullptr;
+    fn_reducescatter reducescatter = nullptr;
     fn_destroy destroy = nullptr;
     fn_errstr errstr = nullptr;
 } api;
@@ -38,6 +42,8 @@ int load(std::string& err) {
     api.get_id = (fn_get_id)dlsym(api.lib, "ncclGetUniqueId");
     api.init_rank = (fn_init_rank)dlsym(api.lib, "ncclCommInitRank");
     api.allreduce = (fn_allreduce)dlsym(api.lib, "ncclAllReduce");
+    api.allgather = (fn_allgather)dlsym(api.lib, "ncclAllGather");
+    api.reducescatter = (fn_reducescatter)dlsym(api.lib, "ncclReduceScatter");
     api.destroy = (fn_destroy)dlsym(api.lib, "ncclCommDestroy");
     api.errstr = (fn_errstr)dlsym(api.lib, "ncclGetErrorString");
     if (!api.get_id || !api.init_rank || !api.allreduce || !api.destroy) { err = "NCCL symbols missing"; return -1; }
@@ -74,6 +80,19 @@ int Comm::allreduce_sum(double* buf, size_t n, cudaStream_t st, std::string& err
 int Comm::allreduce_max(double* buf, size_t n, cudaStream_t st, std::string& err) {
     const int r = api.allreduce(buf, buf, n, NCCL_FLOAT64, NCCL_MAX, comm, st);
     if (r) { err = "ncclAllReduce(max): " + nccl_err(r); return -1; }
+    return 0;
+}
+int Comm::allgather_bytes(const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st, std::string& err) {
+    if (!api.allgather) { err = "ncclAllGather missing"; return -1; }
+    const int r = api.allgather(send, recv, bytes_per_rank, /*ncclChar*/ 0, comm, st);
+    if (r) { err = "ncclAllGather: " + nccl_err(r); return -1; }
+    return 0;
+}
+// recv (count doubles) = sum over ranks of the rank-th slice of send (nranks * count doubles)
+int Comm::reduce_scatter_sum(const double* send, double* recv, size_t count, cudaStream_t st, std::string& err) {
+    if (!api.reducescatter) { err = "ncclReduceScatter missing"; return -1; }
+    const int r = api.reducescatter(send, recv, count, /*ncclFloat64*/ 8, /*ncclSum*/ 0, comm, st);
+    if (r) { err = "ncclReduceScatter: " + nccl_err(r); return -1; }
     return 0;
 }
 void Comm::destroy() {

@@ -82,7 +82,12 @@ struct DevProblem {
     int32_t* ex_tile_of;  // ex_NT * ex_NT: tile index of (I,J), I <= J, or -1
     int32_t* ex_tile_I;   // ex_ntiles
     int32_t* ex_tile_J;   // ex_ntiles
-    double* ex_S;         // ex_ntiles * 384 * 384, row-major tiles
+    double* ex_S;         // row-major 384x384 tiles: all ex_ntiles of them (multi-GPU: this rank's PARTIAL sums, padded to a
+                          // multiple of the rank count for the reduce-scatter)
+    // multi-GPU: the summed tiles are sharded in contiguous ranges; rank r owns the global tiles ex_own0 .. ex_own0+ex_nown-1
+    // in ex_Sown (local tile t = global tile - ex_own0) and applies only those.  Single GPU: ex_Sown = ex_S, all tiles.
+    int32_t ex_own0, ex_nown;
+    double* ex_Sown;
     int32_t* ex_qa;       // ex_ncontrib: q slot of the first observation (smaller camera index), producer (point) order
     int32_t* ex_qb;       // ex_ncontrib: q slot of the second observation
     int32_t* ex_dest;     // ex_ncontrib: position of the contribution in block-sorted order
@@ -91,11 +96,20 @@ struct DevProblem {
     int32_t* ex_blk_off;  // ex_nblocks: first contribution of the block in the block-sorted buffer
     int32_t* ex_blk_len;  // ex_nblocks: run length; the block list is ordered by run length, longest first
     double* ex_contrib;   // 12 * ex_ncontrib: compact contributions (K 3x3, X), block-sorted; expanded to D_i K D_j^T by the assembly
-    double* ex_row;       // ex_ntiles * 384: row partials of the tile mat-vec (y_I += T x_J)
-    double* ex_col;       // ex_ntiles * 6 * 384: column partials per 64-row chunk (y_J += T^T x_I); = ex_row + ex_ntiles * 384
+    double* ex_row;       // ex_nown * 384: row partials of the tile mat-vec (y_I += T x_J), local tile order
+    double* ex_col;       // ex_nown * 6 * 384: column partials per 64-row chunk (y_J += T^T x_I); = ex_row + ex_nown * 384
     int32_t* ex_fold_ptr; // ex_NT + 1
     int32_t* ex_fold_off; // offsets (doubles, relative to ex_row) of the partial vectors of every camera tile, fixed order
     double* cam_Q;        // 12*Nc: Q = (R Jr)^T row-major (9) + pad, written by K0: C = A [X - t]x Q^T
+    // ---- peer-memory all-reduce of the PCG operator partial (multi-GPU; sba_kernels_pcg.cu, PM_XCHG) ----
+    // every rank owns a mailbox, mapped into every process (CUDA IPC, stores travel over NVLink / NVSwitch):
+    //   double   data[2][xchg_n][xchg_stride]     (parity of the exchange number, source rank, vector element)
+    //   uint32_t flag[2][xchg_n][pcg_blocks]      (= exchange number once the source rank's block has pushed its slice)
+    int32_t xchg_n;       // ranks (0 = exchange through NCCL instead)
+    int32_t xchg_rank;
+    int32_t xchg_stride;  // doubles per (parity, source) buffer = pcg_blocks * 192
+    double* xchg_peer[8]; // mailbox base of every rank (own entry = local pointer)
+    uint32_t* xchg_ctr;   // local: number of exchanges completed so far (identical on every rank)
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -137,7 +151,7 @@ struct DevProblem {
 enum { SC_COST = 0, SC_RZ = 1, SC_RZ0 = 2, SC_PQ = 3, SC_MODEL = 4, SC_STEP2 = 5, SC_X2 = 6, SC_GMAX = 7,
        SC_COST_OBS = 8, SC_COST_PRIOR = 9, SC_MODEL_PRIOR = 10, SC_COST_PRIOR_CAM = 11, SC_MODEL_PRIOR_CAM = 12,
        SC_STEP2_CAM = 13, SC_X2_CAM = 14, SC_GMAX_CAM = 15, SC_RZ_NEXT = 16, SC_N = 32 };
-enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, FL_PCG_ITERS_NEXT = 4, FL_N = 8 };
+enum { FL_CHEIRALITY = 0, FL_SINGULAR_PT = 1, FL_NOT_PD = 2, FL_PCG_ITERS = 3, FL_PCG_ITERS_NEXT = 4, FL_XCHG_TIMEOUT = 5, FL_XCHG_DEAD = 6, FL_N = 8 };
 
 // ---- launch wrappers (sba_kernels.cu); all asynchronous on `st` ----
 void launch_pose_cache(const DevProblem& P, cudaStream_t st);
@@ -168,7 +182,18 @@ void launch_zero_fixed(const DevProblem& P, const double* x, double* xz, cudaStr
 void launch_negate(double* x, int n, cudaStream_t st);
 void launch_pcg_init(const DevProblem& P, cudaStream_t st);       // x=0, r=rhs, z=Minv r, p=z, rz, rz0
 int pcg_blocks(const DevProblem& P);
+// PCG step "mode": where the local part of q = S p comes from, whether it is all-reduced through the peer mailboxes
+// inside the kernel, and whether (Hcc + lam) p still has to be added (implicit operator; the explicit tiles contain it)
+enum { PM_SRC_TILES = 0,   // - sum of the camera-pass tile partials (mv_part)
+       PM_SRC_Q = 1,       // pcg_q as it stands (all-reduced by NCCL)
+       PM_SRC_FOLD = 2,    // fold of the explicit mat-vec partials of this rank's tiles
+       PM_SRC_MASK = 3,
+       PM_XCHG = 4,        // sum the local part over the ranks through the peer mailboxes (fused kernel only)
+       PM_HCC = 8 };
 bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st);   // A+B+C in one cooperative launch
+bool pcg_fused_available(const DevProblem& P);
+int pcg_xchg_stride(const DevProblem& P);                               // doubles per (parity, source) mailbox buffer
+size_t pcg_xchg_bytes(const DevProblem& P, int nranks);                 // mailbox size
 void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st);    // q (from tile partials or all-reduced) + p.q partials
 void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z | beta, p (frozen once converged)
 void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st);   // operator pass 2, tile partials only
@@ -183,7 +208,8 @@ void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* l
 void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st);
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
 // explicit reduced camera system
-void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> tiles (needs Hinv, Sd, lam_c of this LM iteration)
+void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> off-diagonal blocks of ex_S (needs Hinv of this LM iteration)
+void launch_explicit_diag(const DevProblem& P, cudaStream_t st);      // diagonal blocks of the owned tiles (needs Hcc, Sd, lam_c; multi-GPU: after the reduce-scatter)
 void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg = 0, double tol2 = 0.0,
                             int max_iters = 0);   // tile partials ex_row / ex_col of S x (pcg: skip once the PCG is frozen)
 void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)

@@ -156,21 +156,30 @@ __global__ void __launch_bounds__(128) k_explicit_assemble(DevProblem P) {
         for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, -B[6 * r + c], -B[6 * r + c + 1]);
 }
 
-// diagonal blocks: S_ii = Hcc + lam - Sd, stored HALVED in the diagonal tiles (T x + T^T x counts them twice)
+// diagonal blocks: S_ii = Hcc + lam - Sd, stored HALVED in the diagonal tiles (T x + T^T x counts them twice).  Written
+// into the OWNED copy of the tile (multi-GPU: after the reduce-scatter of the partial tiles, by the owner only; Hcc and
+// Sd are already all-reduced there)
 __global__ void k_explicit_diag(DevProblem P) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= P.Nc * 36) return;
     const int c = t / 36, e = t - 36 * c, r = e / 6, cc = e - 6 * r;
+    const int I = c / EX_TB;
+    const int tile = P.ex_tile_of[I * P.ex_NT + I] - P.ex_own0;
+    if (tile < 0 || tile >= P.ex_nown) return;
     const int q = sym6(r, cc);
     double v = P.Hcc[21 * (size_t)c + q] - P.Sd[21 * (size_t)c + q];
     if (r == cc) v += P.lam_c[6 * (size_t)c + r];
-    P.ex_S[ex_elem(P, c, c) + (size_t)r * EX_TD + cc] = 0.5 * v;
+    const int l = 6 * (c - I * EX_TB);
+    P.ex_Sown[(size_t)tile * EX_TD * EX_TD + (size_t)(l + r) * EX_TD + l + cc] = 0.5 * v;
 }
 
 void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on) return;
     if (P.ex_ncontrib) k_explicit_contrib<<<cdiv(P.ex_ncontrib, 256), 256, 0, st>>>(P);
     if (P.ex_nblocks) k_explicit_assemble<<<cdiv(P.ex_nblocks, 128), 128, 0, st>>>(P);
+}
+void launch_explicit_diag(const DevProblem& P, cudaStream_t st) {
+    if (!P.ex_on) return;
     k_explicit_diag<<<cdiv(P.Nc * 36, 256), 256, 0, st>>>(P);
 }
 
@@ -205,11 +214,11 @@ __global__ void __launch_bounds__(32 * EX_MVW) k_explicit_matvec(DevProblem P, c
         const double rz = P.scalars[SC_RZ_NEXT], rz0 = P.scalars[SC_RZ0];
         if (!(rz > tol2 * rz0) || !(rz0 > 0.0) || P.flags[FL_PCG_ITERS_NEXT] >= max_iters) return;   // uniform over the grid
     }
-    const int tile = blockIdx.x / EX_NCHUNK, h = blockIdx.x - tile * EX_NCHUNK;
+    const int tile = blockIdx.x / EX_NCHUNK, h = blockIdx.x - tile * EX_NCHUNK;   // local tile of this rank
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int I = __ldg(P.ex_tile_I + tile), J = __ldg(P.ex_tile_J + tile);
+    const int I = __ldg(P.ex_tile_I + P.ex_own0 + tile), J = __ldg(P.ex_tile_J + P.ex_own0 + tile);
     const int n = 6 * P.Nc;
-    const double* T = P.ex_S + (size_t)tile * EX_TD * EX_TD;
+    const double* T = P.ex_Sown + (size_t)tile * EX_TD * EX_TD;
     double xJ[12], col[12];
 #pragma unroll
     for (int k = 0; k < 12; k++) {
@@ -250,7 +259,7 @@ __global__ void __launch_bounds__(32 * EX_MVW) k_explicit_matvec(DevProblem P, c
     }
 }
 void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg, double tol2, int max_iters) {
-    if (P.ex_ntiles) k_explicit_matvec<<<P.ex_ntiles * EX_NCHUNK, 32 * EX_MVW, 0, st>>>(P, x, pcg, tol2, max_iters);
+    if (P.ex_nown) k_explicit_matvec<<<P.ex_nown * EX_NCHUNK, 32 * EX_MVW, 0, st>>>(P, x, pcg, tol2, max_iters);
 }
 
 __global__ void __launch_bounds__(128) k_explicit_gather(DevProblem P, double* y) {

@@ -68,40 +68,82 @@ __device__ __forceinline__ bool pcg_frozen(const DevProblem& P, double tol2, int
     return !(rz > tol2 * rz0) || !(rz0 > 0.0) || P.flags[FL_PCG_ITERS] >= max_iters;
 }
 
-// mode 0: q = -sum tiles + Hcc p + lam p (single GPU);  mode 1: q (all-reduced partial) += Hcc p + lam p;
-// mode 2: q = S p folded from the tile partials of the explicit system (Hcc, lam and the Schur term are all inside S)
+// ---- peer-memory all-reduce of one vector slice per block (multi-GPU, PM_XCHG) ----------------------------------
+// Every rank pushes its block's PCG_BLOCK partial values straight into the mailbox of every peer (plain stores to
+// IPC-mapped memory: NVLink / NVSwitch writes), publishes a per-(source, block) flag with release semantics, waits for
+// the same block of every peer, and sums the G slices in RANK ORDER -- the same order and the same operands on every
+// rank, so q (hence alpha, beta and every later iterate) stays bitwise identical across ranks, as with NCCL's
+// replicated result but without a kernel boundary and a collective launch per PCG iteration.  Buffers alternate with
+// the parity of the exchange number: a rank can be at most one exchange ahead of a peer (it needs the peer's flag of
+// exchange k+1, which the peer sets only after its kernel of exchange k has completed).
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t* xchg_flags(const DevProblem& P, int g) {
+    return reinterpret_cast<uint32_t*>(P.xchg_peer[g] + 2 * (size_t)P.xchg_n * P.xchg_stride);
+}
+// every thread of the block calls it with its own value; i = global element index (< xchg_stride)
+__device__ __forceinline__ double peer_allreduce(const DevProblem& P, double v, int i, uint32_t seq) {
+    const int G = P.xchg_n, me = P.xchg_rank, nb = gridDim.x;
+    const int par = (int)(seq & 1u);
+    const size_t stride = (size_t)P.xchg_stride;
+    for (int g = 0; g < G; g++)
+        if (g != me) __stcg(P.xchg_peer[g] + (size_t)(par * G + me) * stride + i, v);
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < G && (int)threadIdx.x != me) {   // one thread per peer: publish, then wait for that peer
+        const int g = threadIdx.x;
+        st_release_sys(xchg_flags(P, g) + (size_t)(par * G + me) * nb + blockIdx.x, seq);
+        const uint32_t* mine = xchg_flags(P, me) + (size_t)(par * G + g) * nb + blockIdx.x;
+        const long long t0 = clock64();
+        while (ld_acquire_sys(mine) != seq) {
+            if (clock64() - t0 > 6000000000LL) { P.flags[FL_XCHG_TIMEOUT] = 1; break; }   // ~3 s: a peer died; the host reports it
+        }
+    }
+    __syncthreads();
+    double acc = 0.0;
+    for (int g = 0; g < G; g++)
+        acc += g == me ? v : __ldcg(P.xchg_peer[me] + (size_t)(par * G + g) * stride + i);
+    return acc;
+}
+
+// local part of q_i = (S p)_i according to the mode (see PM_* in sba_device.h); block-uniform barriers inside
+__device__ __forceinline__ double pcg_local_q(const DevProblem& P, int mode, int i, int n, int* s_off) {
+    const int src = mode & PM_SRC_MASK;
+    if (src == PM_SRC_FOLD) return explicit_fold(P, i, i < n, s_off);
+    if (i >= n) return 0.0;
+    if (src == PM_SRC_Q) return P.pcg_q[i];
+    const int c = i / 6, a = i - 6 * c;
+    double acc = 0.0;
+    if (!P.cam_fixed[c]) acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
+    return -acc;
+}
+__device__ __forceinline__ double pcg_hcc_p(const DevProblem& P, int i) {   // ((Hcc + lam) p)_i
+    const int c = i / 6, a = i - 6 * c;
+    const double* p = P.pcg_p + 6 * (size_t)c;
+    const double* H = P.Hcc + 21 * (size_t)c;
+    double hx = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
+    return hx + P.lam_c[i] * p[a];
+}
+
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_A(DevProblem P, int mode) {
     __shared__ double sh[33];
     __shared__ int s_off[PCG_BLOCK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
-    double folded = 0.0;
-    if (mode == 2) folded = explicit_fold(P, i, i < n, s_off);   // block-uniform branch (barriers inside)
+    double q_i = pcg_local_q(P, mode, i, n, s_off);
     if (i == 0) { P.scalars[SC_RZ] = P.scalars[SC_RZ_NEXT]; P.flags[FL_PCG_ITERS] = P.flags[FL_PCG_ITERS_NEXT]; }
     double pq = 0.0;
     if (i < n) {
-        const int c = i / 6, a = i - 6 * c;
-        double acc = 0.0;
-        if (mode == 2) {
-        } else if (mode == 0) {
-            if (!P.cam_fixed[c]) {
-                acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
-            }
-            acc = -acc;
-        } else {
-            acc = P.pcg_q[i];
-        }
-        const double* p = P.pcg_p + 6 * (size_t)c;
-        if (mode == 2) {
-            acc = folded;
-        } else {
-            const double* H = P.Hcc + 21 * (size_t)c;
-            double hx = 0.0;
-#pragma unroll
-            for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
-            acc += hx + P.lam_c[i] * p[a];
-        }
-        P.pcg_q[i] = acc;
-        pq = p[a] * acc;
+        if (mode & PM_HCC) q_i += pcg_hcc_p(P, i);
+        P.pcg_q[i] = q_i;
+        pq = P.pcg_p[i] * q_i;
     }
     pq = block_sum(pq, sh);
     if (threadIdx.x == 0) P.pcg_part[blockIdx.x] = pq;
@@ -159,42 +201,24 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
     __shared__ double sr[PCG_BLOCK];
     __shared__ int s_off[PCG_BLOCK];
     const int i = blockIdx.x * blockDim.x + threadIdx.x, n = 6 * P.Nc;
-    double folded = 0.0;
-    if (mode == 2) folded = explicit_fold(P, i, i < n, s_off);   // block-uniform branch (barriers inside)
     // ---- A (reads the scalars of the previous iteration through the NEXT copies: nobody writes them before the last barrier)
     const double rz = P.scalars[SC_RZ_NEXT], rz0 = P.scalars[SC_RZ0];
     const int it = P.flags[FL_PCG_ITERS_NEXT];
     const bool frozen = !(rz > tol2 * rz0) || !(rz0 > 0.0) || it >= max_iters;
-    double pq = 0.0, p_i = 0.0, q_i = 0.0;
+    if (frozen) return;   // uniform over the grid AND over the ranks (replicated scalars): no barrier, no exchange
+    if ((mode & PM_XCHG) && P.flags[FL_XCHG_DEAD]) return;   // an earlier launch timed out on a peer (set after its last barrier: uniform)
+    const uint32_t seq = (mode & PM_XCHG) ? *P.xchg_ctr + 1u : 0u;   // (written only after the last barrier)
+    double q_i = pcg_local_q(P, mode, i, n, s_off);
+    if (mode & PM_XCHG) q_i = peer_allreduce(P, q_i, i, seq);
+    double pq = 0.0, p_i = 0.0;
     if (i < n) {
-        const int c = i / 6, a = i - 6 * c;
-        double acc = 0.0;
-        if (mode == 2) {
-        } else if (mode == 0) {
-            if (!P.cam_fixed[c]) {
-                acc = sum_partials(P.mv_part, P.cam_tile_off[c], P.cam_tile_off[c + 1], a);
-            }
-            acc = -acc;
-        } else {
-            acc = P.pcg_q[i];
-        }
-        const double* p = P.pcg_p + 6 * (size_t)c;
-        p_i = p[a];
-        if (mode == 2) {
-            q_i = folded;
-        } else {
-            const double* H = P.Hcc + 21 * (size_t)c;
-            double hx = 0.0;
-#pragma unroll
-            for (int b = 0; b < 6; b++) hx += H[sym6(a, b)] * p[b];
-            q_i = acc + (hx + P.lam_c[i] * p_i);
-        }
+        p_i = P.pcg_p[i];
+        if (mode & PM_HCC) q_i += pcg_hcc_p(P, i);
         P.pcg_q[i] = q_i;
         pq = p_i * q_i;
     }
     pq = block_sum(pq, sh);
     if (threadIdx.x == 0) P.pcg_part[blockIdx.x] = pq;
-    if (frozen) return;   // uniform over the grid: no barrier is reached by anyone
     grid.sync();
     // ---- B
     const double alpha = rz / fold_partials(P.pcg_part, nb, sh);
@@ -231,12 +255,16 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
     if (i == 0) {
         P.scalars[SC_RZ] = rz; P.flags[FL_PCG_ITERS] = it;
         P.scalars[SC_RZ_NEXT] = rz_new; P.flags[FL_PCG_ITERS_NEXT] = it + 1;
+        if (mode & PM_XCHG) { *P.xchg_ctr = seq; if (P.flags[FL_XCHG_TIMEOUT]) P.flags[FL_XCHG_DEAD] = 1; }
     }
 }
 
 int pcg_blocks(const DevProblem& P) { return cdiv(6 * P.Nc, PCG_BLOCK); }
-// returns false when the cooperative path is unavailable (caller falls back to A + B + C)
-bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st) {
+int pcg_xchg_stride(const DevProblem& P) { return pcg_blocks(P) * PCG_BLOCK; }
+size_t pcg_xchg_bytes(const DevProblem& P, int nranks) {
+    return 2 * (size_t)nranks * pcg_xchg_stride(P) * sizeof(double) + 2 * (size_t)nranks * pcg_blocks(P) * sizeof(uint32_t);
+}
+static int pcg_coop_blocks() {
     static int ok_blocks = -1;
     if (ok_blocks < 0) {
         int dev = 0, coop = 0, sms = 0, per_sm = 0;
@@ -246,8 +274,13 @@ bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters,
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_ABC, PCG_BLOCK, 0);
         ok_blocks = coop ? sms * per_sm : 0;
     }
+    return ok_blocks;
+}
+bool pcg_fused_available(const DevProblem& P) { return pcg_blocks(P) <= pcg_coop_blocks(); }
+// returns false when the cooperative path is unavailable (caller falls back to A + B + C; PM_XCHG needs the fused kernel)
+bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st) {
     int nb = pcg_blocks(P);
-    if (nb > ok_blocks) return false;
+    if (nb > pcg_coop_blocks()) return false;
     DevProblem Pc = P;
     void* args[] = {&Pc, &mode, &tol2, &max_iters, &nb};
     return cudaLaunchCooperativeKernel((void*)k_pcg_ABC, dim3(nb), dim3(PCG_BLOCK), args, 0, st) == cudaSuccess;

@@ -67,12 +67,19 @@ __global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
     double v[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (pt >= 0) {   // padding: planes stay zero
         const int cam = __ldcs(P.q_cam + q);
-        const double2 x01 = ldg2(P.pts + 4 * (size_t)pt), x23 = ldg2(P.pts + 4 * (size_t)pt + 2);
-        const double X[3] = {x01.x, x01.y, x23.x};
+        const d4 Xp = ld256(P.pts + 4 * (size_t)pt);
+        const double X[3] = {Xp.x, Xp.y, Xp.z};
         const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+        // only Rt and t are needed (C is not kept in point order: its expressions, hence Jr, are dead code here):
+        // three 256-bit gathers instead of eleven 128-bit ones
         double ccr[22];
+        {
+            const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
+            ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
+            ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
 #pragma unroll
-        for (int i = 0; i < 11; i++) { const double2 t = ldg2(cc + 2 * i); ccr[2 * i] = t.x; ccr[2 * i + 1] = t.y; }
+            for (int i = 12; i < 22; i++) ccr[i] = 0.0;
+        }
         const double* in = P.intr + 10 * __ldg(P.cam_model + cam);
         double intr[10];
 #pragma unroll

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace sba {
@@ -23,6 +24,8 @@ namespace sba {
 Solver::Solver(const sba_options& o) : opt(o) {}
 
 Solver::~Solver() {
+    if (st) cudaStreamSynchronize(st);
+    release_peer_exchange();
     comm.destroy();
     timer.destroy();
     arena.release();

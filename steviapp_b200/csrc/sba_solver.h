@@ -22,6 +22,8 @@ struct Comm {
     int init(int rank, int nranks, const uint8_t* id128, std::string& err);
     int allreduce_sum(double* buf, size_t n, cudaStream_t st, std::string& err);
     int allreduce_max(double* buf, size_t n, cudaStream_t st, std::string& err);
+    int reduce_scatter_sum(const double* send, double* recv, size_t count, cudaStream_t st, std::string& err);
+    int allgather_bytes(const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st, std::string& err);
     void destroy();
     static int unique_id(uint8_t* id128, std::string& err);
 };
@@ -101,6 +103,7 @@ private:
     int build_rhs_and_preconditioner(bool* ok);            // damped inverse, reduced rhs, Minv
     int schur_apply(const double* x, double* y);           // y = S x  (x zero at fixed cameras)
     int run_pcg(int* iters);
+    int setup_peer_exchange();               // sba_solver_hooks.inc: IPC mailboxes of the fused PCG all-reduce (multi-GPU)
     int build_explicit_structure(const std::vector<int32_t>& pt_cnt, const std::vector<int32_t>& pt_q0,
                                  const std::vector<int32_t>& q_cam);   // sba_solver_explicit.inc
 
@@ -127,6 +130,9 @@ private:
     PhaseTimer timer;
     int launches = 0;
     bool scaling_done = false;
+    void* xchg_mailbox = nullptr;  // this rank's mailbox of the peer-memory all-reduce (own cudaMalloc: exported through CUDA IPC)
+    std::vector<void*> ipc_opened; // peer mailboxes opened with cudaIpcOpenMemHandle
+    void release_peer_exchange();
 };
 
 }  // namespace sba
