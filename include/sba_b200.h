@@ -197,7 +197,8 @@ int sba_set_options(sba_solver* s, const sba_options* o);
  * stage: 0 = K1 residual+Jacobian, 1 = K1c cost only, 2 = K1p/K2a (fused) + K2b, 3 = reduced-system mat-vec (the
  * operator the PCG applies: explicit tiles or implicit passes), 4 = preconditioner build, 5 = K1p/K2a, 6 = implicit
  * point pass, 7 = implicit camera pass, 9 = K2b camera blocks, 10 = explicit tile mat-vec kernel, 11 = explicit build
- * (contributions + assembly + diagonal). */
+ * (contributions + assembly), 12 = fused PCG vector kernel alone, 13 = one whole PCG iteration (tile mat-vec + fused
+ * kernel). */
 int sba_time_stage(sba_solver* s, int32_t stage, int32_t reps, double* ms_per_launch);
 
 /* Batched multi-view DLT triangulation (adjacent to the LM loop; reference has

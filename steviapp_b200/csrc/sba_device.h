@@ -104,12 +104,27 @@ struct DevProblem {
     // ---- peer-memory all-reduce of the PCG operator partial (multi-GPU; sba_kernels_pcg.cu, PM_XCHG) ----
     // every rank owns a mailbox, mapped into every process (CUDA IPC, stores travel over NVLink / NVSwitch):
     //   double   data[2][xchg_n][xchg_stride]     (parity of the exchange number, source rank, vector element)
-    //   uint32_t flag[2][xchg_n][pcg_blocks]      (= exchange number once the source rank's block has pushed its slice)
+    //   uint32_t flag[2][xchg_n][xchg_nflag]      (= exchange number once the source rank's block has pushed its slice)
     int32_t xchg_n;       // ranks (0 = exchange through NCCL instead)
     int32_t xchg_rank;
-    int32_t xchg_stride;  // doubles per (parity, source) buffer = pcg_blocks * 192
+    int32_t xchg_stride;  // doubles per (parity, source) buffer: max(pcg_blocks * 192, ps_nitems * 128)
+    int32_t xchg_nflag;   // flags per (parity, source): max(pcg_blocks, ps_nitems)
     double* xchg_peer[8]; // mailbox base of every rank (own entry = local pointer)
     uint32_t* xchg_ctr;   // local: number of exchanges completed so far (identical on every rank)
+    // ---- persistent PCG kernel (sba_kernels_pcgsolve.cu): static schedule of the tile mat-vec and of the fold ----
+    int32_t ps_on;        // 1: run_pcg launches k_pcg_solve once per LM iteration
+    int32_t ps_grid;      // resident CTAs (1 per SM)
+    int32_t ps_nseg;      // segments = runs of 8-row groups inside one tile
+    int32_t ps_nitems;    // items of 96 vector elements (16 cameras), item b owned by CTA b
+    int32_t* ps_seg_ptr;  // ps_grid + 1: segments of CTA b
+    int32_t* ps_seg;      // 4 per segment: local tile, first 8-row group, end group, pad
+    double* ps_part;      // ex_nown * 384 row partials (local tile, row), then ps_nseg * 384 column partials (segment, column)
+    int32_t* ps_fold_ptr; // ex_NT + 1
+    int32_t* ps_fold_off; // per camera tile K: offsets into ps_part of the partial vectors that contribute to K, fixed order
+    double* ps_pq;        // ps_grid: per-CTA part of p^T S p / 2
+    double* ps_rz;        // ps_nitems: per-item part of r.z
+    double* ps_clock;     // 4: ns CTA 0 spent in (mat-vec, barrier 1, fold + vector part, barrier 2) during the last solve
+    double* pcg_p2;       // 6*Nc: second copy of p (directions alternate between pcg_p and pcg_p2)
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -192,6 +207,11 @@ enum { PM_SRC_TILES = 0,   // - sum of the camera-pass tile partials (mv_part)
        PM_HCC = 8 };
 bool launch_pcg_fused(const DevProblem& P, int mode, double tol2, int max_iters, cudaStream_t st);   // A+B+C in one cooperative launch
 bool pcg_fused_available(const DevProblem& P);
+int pcg_solve_grid();                                                   // resident CTAs of the persistent PCG kernel (0 = unavailable)
+int pcg_solve_items(int n_cams);
+int pcg_solve_slot();                                                   // mailbox doubles per item
+bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // whole PCG solve, one cooperative launch
+int pcg_xchg_nflag(const DevProblem& P);
 int pcg_xchg_stride(const DevProblem& P);                               // doubles per (parity, source) mailbox buffer
 size_t pcg_xchg_bytes(const DevProblem& P, int nranks);                 // mailbox size
 void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st);    // q (from tile partials or all-reduced) + p.q partials

@@ -9,6 +9,8 @@
 // reproducible, and identical on every rank of a multi-GPU run.
 #include <cooperative_groups.h>
 
+#include <algorithm>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -89,7 +91,7 @@ __device__ __forceinline__ uint32_t* xchg_flags(const DevProblem& P, int g) {
 }
 // every thread of the block calls it with its own value; i = global element index (< xchg_stride)
 __device__ __forceinline__ double peer_allreduce(const DevProblem& P, double v, int i, uint32_t seq) {
-    const int G = P.xchg_n, me = P.xchg_rank, nb = gridDim.x;
+    const int G = P.xchg_n, me = P.xchg_rank, nb = P.xchg_nflag;
     const int par = (int)(seq & 1u);
     const size_t stride = (size_t)P.xchg_stride;
     for (int g = 0; g < G; g++)
@@ -260,9 +262,10 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
 }
 
 int pcg_blocks(const DevProblem& P) { return cdiv(6 * P.Nc, PCG_BLOCK); }
-int pcg_xchg_stride(const DevProblem& P) { return pcg_blocks(P) * PCG_BLOCK; }
+int pcg_xchg_nflag(const DevProblem& P) { return std::max(pcg_blocks(P), pcg_solve_items(P.Nc)); }
+int pcg_xchg_stride(const DevProblem& P) { return std::max(pcg_blocks(P) * PCG_BLOCK, pcg_solve_items(P.Nc) * pcg_solve_slot()); }
 size_t pcg_xchg_bytes(const DevProblem& P, int nranks) {
-    return 2 * (size_t)nranks * pcg_xchg_stride(P) * sizeof(double) + 2 * (size_t)nranks * pcg_blocks(P) * sizeof(uint32_t);
+    return 2 * (size_t)nranks * pcg_xchg_stride(P) * sizeof(double) + 2 * (size_t)nranks * pcg_xchg_nflag(P) * sizeof(uint32_t);
 }
 static int pcg_coop_blocks() {
     static int ok_blocks = -1;

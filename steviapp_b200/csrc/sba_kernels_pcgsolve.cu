@@ -1,0 +1,387 @@
+// sba_kernels_pcgsolve.cu -- the WHOLE reduced-system solve in one persistent cooperative kernel.
+//
+// Same SCHUR_JACOBI preconditioned CG as sba_kernels_pcg.cu (the loop ceres::Solve runs for ITERATIVE_SCHUR behind
+// modularsbasolver.cpp:938; in-tree analogue modules/g2o/g2o/solvers/pcg/linear_solver_pcg.hpp:84-165) on the explicit
+// tiles of sba_kernels_explicit.cu, but the ~135 iterations of a Venice-scale LM step no longer cost two kernel
+// launches, five grid-wide dependencies and a host poll each:
+//
+//   * one launch per LM iteration; one CTA per SM stays resident and loops over the CG iterations;
+//   * the tile mat-vec is split STATICALLY into equal runs of 8-row groups (one run per CTA, cut into segments at
+//     tile boundaries), so all CTAs finish together -- no wave quantisation, and a rank that owns only a few tiles
+//     (8 GPUs: 51) still fills every SM;
+//   * a CTA's run is ONE contiguous byte range of the tile array: a producer warp streams it with 12 KB bulk
+//     copies (cp.async.bulk -> shared memory, mbarrier complete_tx) through a 16-stage / 192 KB ring, so the bytes in
+//     flight per SM are set by shared memory, not by registers; the 8 consumer warps each own two stages (a private
+//     double buffer of 4-row half groups) and do the two FMAs per element from shared memory;
+//   * p.q = p^T S p is accumulated by the mat-vec itself (2 sum_rows x_I[r] (T x_J)[r]), so alpha needs no second
+//     grid-wide reduction: TWO grid barriers per CG iteration (after the mat-vec, after r.z);
+//   * p is never re-broadcast: the mat-vec rebuilds p = z + beta p_old on the fly (same expression, same bits as the
+//     owner's copy), so there is no barrier between the direction update and the next mat-vec;
+//   * x, r, z, p and the preconditioner rows of an element live in the registers of its owner thread for the whole
+//     solve (one "item" of 96 elements = 16 cameras per CTA);
+//   * multi-GPU: the item's 96 partial q values and the rank's p.q partial go to the peers' mailboxes with plain
+//     NVLink stores and are summed in rank order (see peer exchange in sba_kernels_pcg.cu) -- inside the same kernel.
+//
+// Determinism: static schedule, fixed-shape trees, fixed list orders; no floating-point atomics.  All ranks compute
+// bitwise identical scalars, so the loop exits are uniform across CTAs and ranks.
+#include <cooperative_groups.h>
+
+#include <algorithm>
+
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+namespace cg = cooperative_groups;
+
+constexpr int PS_CWARPS = 8;                    // consumer warps
+constexpr int PS_THREADS = 32 * (PS_CWARPS + 1);   // + one producer warp
+constexpr int PS_ITEM = 96;        // vector elements per item (16 cameras; divides the 384 of a camera tile)
+constexpr int PS_CHAINS = PS_THREADS / PS_ITEM;   // 3 fold chains per element: all 288 threads fold
+constexpr int PS_SLOT = 128;       // mailbox doubles per item: 96 q values + the p.q partial
+constexpr int PS_STAGES = 2 * PS_CWARPS;        // ring stages, two per consumer warp
+constexpr int PS_HALF_ROWS = 4;                 // rows per stage
+constexpr uint32_t PS_STAGE_BYTES = PS_HALF_ROWS * EX_TD * sizeof(double);   // 12288
+static_assert(PS_THREADS == PS_CHAINS * PS_ITEM, "fold roles cover the CTA");
+
+struct PsSmem {
+    double ring[PS_STAGES][PS_HALF_ROWS * EX_TD];   // 192 KB
+    double col[PS_CWARPS][EX_TD];                   // column partials of the consumer warps of one segment
+    double xI[EX_TD];                               // p of the segment's row tile
+    double v[PS_CHAINS][PS_ITEM];                   // chain sums of the fold / r of the item
+    double sh[33];
+    double pq;
+    double pqw[PS_CWARPS];
+    unsigned long long full[PS_STAGES], empty[PS_STAGES];
+};
+
+__device__ __forceinline__ uint32_t ps_saddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void ps_mbar_init(unsigned long long* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(ps_saddr(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void ps_mbar_expect_tx(unsigned long long* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(ps_saddr(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ps_mbar_arrive(unsigned long long* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(ps_saddr(b)) : "memory");
+}
+__device__ __forceinline__ void ps_mbar_wait(unsigned long long* b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" :: "r"(ps_saddr(b)), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared (TMA engine, no tensor map: the source run is contiguous), completion on the mbarrier
+__device__ __forceinline__ void ps_bulk_load(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(ps_saddr(dst)), "l"(src), "r"(bytes), "r"(ps_saddr(bar)) : "memory");
+}
+__device__ __forceinline__ void ps_consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(32 * PS_CWARPS) : "memory"); }
+
+__device__ __forceinline__ uint32_t ps_ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ps_st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+// p = z + beta p_old, the ONE expression used by the owners and by every mat-vec CTA (no contraction: same bits)
+__device__ __forceinline__ double ps_dir(double z, double beta, double p_old) { return __dadd_rn(z, __dmul_rn(beta, p_old)); }
+
+// fold of a per-CTA partial array (written by other CTAs of this launch: L1 bypassed); same value in every thread
+__device__ __forceinline__ double ps_fold(const double* part, int n, double* sh) {
+    double v = 0.0;
+    for (int k = threadIdx.x; k < n; k += PS_THREADS) v += __ldcg(part + k);
+    return block_sum(v, sh);
+}
+
+__device__ __forceinline__ double ps_warp_sum8(const double (&v)[8], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    double r[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = (b4 ? v[4 + i] : v[i]) + __shfl_xor_sync(FULL, b4 ? v[i] : v[4 + i], 16);
+    double p[2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) p[i] = (b3 ? r[2 + i] : r[i]) + __shfl_xor_sync(FULL, b3 ? r[i] : r[2 + i], 8);
+    double q = (b2 ? p[1] : p[0]) + __shfl_xor_sync(FULL, b2 ? p[0] : p[1], 4);
+    q += __shfl_xor_sync(FULL, q, 2);
+    q += __shfl_xor_sync(FULL, q, 1);
+    return q;   // total of value (lane >> 2) in every lane
+}
+
+__global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters) {
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(128) unsigned char ps_smem_raw[];
+    PsSmem& sm = *reinterpret_cast<PsSmem*>(ps_smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, b = blockIdx.x;
+    const bool producer = warp == PS_CWARPS;
+    const int n = 6 * P.Nc;
+    const int G = P.xchg_n, me = P.xchg_rank;
+    if (tid == 0) {
+        for (int s = 0; s < PS_STAGES; s++) { ps_mbar_init(&sm.full[s], 1); ps_mbar_init(&sm.empty[s], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // ---- owner role: item b = elements 96 b .. 96 b + 95, thread tid < 96 owns element i
+    const bool has_item = b < P.ps_nitems;
+    const int e = tid % PS_ITEM, ch = tid / PS_ITEM;   // fold role: element e, chain ch
+    const int i = b * PS_ITEM + e;
+    const bool owner = has_item && tid < PS_ITEM && i < n;
+    const int a6 = i % 6;
+    double x_i = 0.0, r_i = 0.0, z_i = 0.0, p_i = 0.0, M[6] = {0, 0, 0, 0, 0, 0};
+    if (owner) {
+        const double* Mr = P.Minv + 36 * (size_t)(i / 6) + 6 * a6;
+#pragma unroll
+        for (int k = 0; k < 6; k++) M[k] = Mr[k];
+        r_i = P.rhs[i];
+    }
+    // z = Minv r of the item (r of the other elements of the camera through shared memory), and the item's r.z
+    auto precondition = [&]() -> double {
+        __syncthreads();
+        if (tid < PS_ITEM) sm.v[0][tid] = r_i;
+        __syncthreads();
+        double rz = 0.0;
+        if (owner) {
+            const double* rc = &sm.v[0][e - a6];
+            double z = 0.0;
+#pragma unroll
+            for (int k = 0; k < 6; k++) z += M[k] * rc[k];
+            z_i = z;
+            __stcg(P.pcg_z + i, z);
+            rz = r_i * z;
+        }
+        return block_sum(rz, sm.sh);
+    };
+    // ---- init: x = 0, r = rhs, z = Minv r, p = z (beta = 0 with p_old = z), rz0 = r.z
+    {
+        const double rzp = precondition();
+        if (owner) { p_i = z_i; __stcg(P.pcg_p + i, z_i); }
+        if (has_item && tid == 0) __stcg(P.ps_rz + b, rzp);
+    }
+    __threadfence();
+    grid.sync();
+    double rz = ps_fold(P.ps_rz, P.ps_nitems, sm.sh);
+    const double rz0 = rz;
+    double beta = 0.0;
+    int it = 0, cur = 0;
+    uint32_t seq = G > 1 ? *P.xchg_ctr : 0u;
+    const int seg0 = P.ps_seg_ptr[b], seg1 = P.ps_seg_ptr[b + 1];
+    const size_t colbase = (size_t)P.ex_nown * EX_TD;
+    // this CTA's run: groups gb0 .. gb0 + ng - 1 of the rank's 8-row groups = one contiguous byte range of the tiles
+    int ng = 0;
+    const double* run = nullptr;
+    if (seg1 > seg0) {
+        const int4 S0 = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + seg0);
+        run = P.ex_Sown + ((size_t)S0.x * 48 + S0.y) * 8 * EX_TD;
+        for (int sg = seg0; sg < seg1; sg++) { const int4 S = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + sg); ng += S.z - S.y; }
+    }
+    unsigned int jdone = 0;   // groups streamed in the previous iterations: stage = (2 * group number + half) % 16
+    // phase clock of CTA 0 (ns, summed over the iterations): mat-vec, barrier 1, fold + vector part, barrier 2 + scalars
+    auto now = [&]() -> long long { long long t = 0; if (b == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
+    long long t_m = 0, t_s1 = 0, t_f = 0, t_s2 = 0, t_a = now();
+
+    while (rz > tol2 * rz0 && rz0 > 0.0 && it < max_iters) {
+        const double* p_old = cur ? P.pcg_p2 : P.pcg_p;
+        double* p_new = cur ? P.pcg_p : P.pcg_p2;
+        // ---- direction of this iteration (owner copy; the mat-vec below rebuilds the same values from z, beta, p_old)
+        if (owner) { p_i = ps_dir(z_i, beta, p_i); __stcg(p_new + i, p_i); }
+        // ---- M: tile mat-vec over this CTA's run
+        if (producer) {
+            if (lane == 0) {
+                for (unsigned int h = 0; h < 2u * ng; h++) {
+                    const unsigned int H = 2u * jdone + h, s = H % PS_STAGES, use = H / PS_STAGES;
+                    if (use > 0) ps_mbar_wait(&sm.empty[s], (use - 1) & 1u);   // the owner warp has released the previous contents
+                    ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
+                    ps_bulk_load(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s]);
+                }
+            }
+        } else {
+            double pq_lane = 0.0;
+            unsigned int jseg = jdone;   // number of the first group of the segment
+            for (int sg = seg0; sg < seg1; sg++) {
+                const int4 S = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + sg);   // local tile, first group, end group
+                const int tile = S.x, g0 = S.y, g1 = S.z;
+                const int I = __ldg(P.ex_tile_I + P.ex_own0 + tile), J = __ldg(P.ex_tile_J + P.ex_own0 + tile);
+                ps_consumer_sync();   // xI / col of the previous segment are free
+                for (int r = 8 * g0 + tid; r < 8 * g1; r += 32 * PS_CWARPS) {
+                    const int gi = EX_TD * I + r;
+                    sm.xI[r] = gi < n ? ps_dir(__ldcg(P.pcg_z + gi), beta, __ldcg(p_old + gi)) : 0.0;
+                }
+                double xJ[12], col[12];
+#pragma unroll
+                for (int k = 0; k < 12; k++) {
+                    const int gj = EX_TD * J + lane + 32 * k;
+                    xJ[k] = gj < n ? ps_dir(__ldcg(P.pcg_z + gj), beta, __ldcg(p_old + gj)) : 0.0;
+                    col[k] = 0.0;
+                }
+                ps_consumer_sync();
+                // groups of the segment whose number is = warp (mod 8)
+                const unsigned int first = (warp + PS_CWARPS - (jseg % PS_CWARPS)) % PS_CWARPS;
+                for (unsigned int o = first; o < (unsigned int)(g1 - g0); o += PS_CWARPS) {
+                    const unsigned int j = jseg + o;
+                    const uint32_t parity = (j / PS_CWARPS) & 1u;   // use number of the warp's two stages
+                    const int row0 = 8 * (g0 + (int)o);
+                    double racc[8];
+#pragma unroll
+                    for (int hf = 0; hf < 2; hf++) {
+                        const int s = 2 * warp + hf;
+                        ps_mbar_wait(&sm.full[s], parity);
+                        const double* buf = sm.ring[s];
+#pragma unroll
+                        for (int rr = 0; rr < PS_HALF_ROWS; rr++) {
+                            const double xi = sm.xI[row0 + 4 * hf + rr];   // warp-uniform
+                            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+                            for (int k = 0; k < 12; k += 2) {
+                                const double v0 = buf[rr * EX_TD + lane + 32 * k], v1 = buf[rr * EX_TD + lane + 32 * (k + 1)];
+                                acc0 += v0 * xJ[k]; acc1 += v1 * xJ[k + 1];
+                                col[k] += v0 * xi; col[k + 1] += v1 * xi;
+                            }
+                            racc[4 * hf + rr] = acc0 + acc1;
+                        }
+                        __syncwarp();
+                        if (lane == 0) ps_mbar_arrive(&sm.empty[s]);
+                    }
+                    const double s8 = ps_warp_sum8(racc, lane);
+                    if ((lane & 3) == 0) {
+                        const int r = row0 + (lane >> 2);
+                        __stcg(P.ps_part + (size_t)tile * EX_TD + r, s8);
+                        pq_lane += sm.xI[r] * s8;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 12; k++) sm.col[warp][lane + 32 * k] = col[k];
+                ps_consumer_sync();
+                for (int c = tid; c < EX_TD; c += 32 * PS_CWARPS) {
+                    double acc = sm.col[0][c];
+#pragma unroll
+                    for (int w = 1; w < PS_CWARPS; w++) acc += sm.col[w][c];   // warp order: fixed
+                    __stcg(P.ps_part + colbase + (size_t)sg * EX_TD + c, acc);
+                }
+                jseg += (unsigned int)(g1 - g0);
+            }
+            // this CTA's part of p^T S p / 2: warp trees, then the warps in order
+            pq_lane = warp_sum(pq_lane);
+            if (lane == 0) sm.pqw[warp] = pq_lane;
+        }
+        jdone += (unsigned int)ng;
+        __syncthreads();
+        if (tid == 0) {
+            double v = sm.pqw[0];
+#pragma unroll
+            for (int w = 1; w < PS_CWARPS; w++) v += sm.pqw[w];
+            __stcg(P.ps_pq + b, v);
+        }
+        long long t_b = now(); t_m += t_b - t_a;
+        __threadfence();
+        grid.sync();
+        t_a = now(); t_s1 += t_a - t_b;
+        // ---- F: q of the item (fold of the partials that touch its camera tile), alpha, x, r, z, item part of r.z
+        if (has_item) {
+            const int K = (b * PS_ITEM) / EX_TD;
+            const int m0 = __ldg(P.ps_fold_ptr + K), m1 = __ldg(P.ps_fold_ptr + K + 1);
+            {   // chain ch sums the entries m0 + ch, m0 + ch + 3, ... in list order
+                const double* base = P.ps_part + (b * PS_ITEM - K * EX_TD + e);
+                double acc = 0.0;
+                int m = m0 + ch;
+                for (; m + 15 * PS_CHAINS < m1; m += 16 * PS_CHAINS) {   // 16 loads in flight
+                    double v[16];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) v[k] = __ldcg(base + __ldg(P.ps_fold_off + m + PS_CHAINS * k));
+#pragma unroll
+                    for (int k = 0; k < 16; k++) acc += v[k];
+                }
+                for (; m < m1; m += PS_CHAINS) acc += __ldcg(base + __ldg(P.ps_fold_off + m));
+                sm.v[ch][e] = acc;
+            }
+            double pq = ps_fold(P.ps_pq, gridDim.x, sm.sh);   // this rank's p^T S p / 2 (barriers inside: sm.v is visible below)
+            double q_i = 0.0;
+            if (tid < PS_ITEM) q_i = (sm.v[0][tid] + sm.v[1][tid]) + sm.v[2][tid];
+            if (G > 1) {   // sum q and p.q over the ranks, rank order, through the peer mailboxes
+                seq++;
+                const int par = (int)(seq & 1u);
+                const size_t stride = (size_t)P.xchg_stride;
+                const double mine = tid < PS_ITEM ? q_i : pq;
+                if (tid <= PS_ITEM) {
+                    for (int g = 0; g < G; g++)
+                        if (g != me) __stcg(P.xchg_peer[g] + (size_t)(par * G + me) * stride + (size_t)b * PS_SLOT + tid, mine);
+                }
+                __threadfence_system();
+                __syncthreads();
+                if (tid < G && tid != me) {
+                    const int g = tid;
+                    uint32_t* fl_g = reinterpret_cast<uint32_t*>(P.xchg_peer[g] + 2 * (size_t)G * stride);
+                    const uint32_t* fl_me = reinterpret_cast<const uint32_t*>(P.xchg_peer[me] + 2 * (size_t)G * stride);
+                    ps_st_release_sys(fl_g + (size_t)(par * G + me) * P.xchg_nflag + b, seq);
+                    const uint32_t* w = fl_me + (size_t)(par * G + g) * P.xchg_nflag + b;
+                    const long long t0 = clock64();
+                    while (ps_ld_acquire_sys(w) != seq)
+                        if (clock64() - t0 > 6000000000LL) { P.flags[FL_XCHG_TIMEOUT] = 1; break; }   // ~3 s: a peer died
+                }
+                __syncthreads();
+                if (tid <= PS_ITEM) {
+                    double acc = 0.0;
+                    for (int g = 0; g < G; g++)
+                        acc += g == me ? mine : __ldcg(P.xchg_peer[me] + (size_t)(par * G + g) * stride + (size_t)b * PS_SLOT + tid);
+                    if (tid < PS_ITEM) q_i = acc; else sm.pq = acc;
+                }
+                __syncthreads();
+                pq = sm.pq;
+            }
+            const double alpha = rz / (2.0 * pq);
+            if (owner) { x_i += alpha * p_i; r_i -= alpha * q_i; }
+            const double rzp = precondition();
+            if (tid == 0) __stcg(P.ps_rz + b, rzp);
+        }
+        t_b = now(); t_f += t_b - t_a;
+        __threadfence();
+        grid.sync();
+        // ---- beta and the convergence scalars: every CTA folds the same partials in the same order
+        const double rz_new = ps_fold(P.ps_rz, P.ps_nitems, sm.sh);
+        beta = rz_new / rz;
+        rz = rz_new;
+        it++;
+        cur ^= 1;
+        t_a = now(); t_s2 += t_a - t_b;
+        if (G > 1 && *reinterpret_cast<volatile int32_t*>(P.flags + FL_XCHG_TIMEOUT)) break;   // set before the barrier: uniform
+    }
+    if (owner) P.pcg_x[i] = x_i;
+    if (b == 0 && tid == 0) {
+        P.scalars[SC_RZ] = rz; P.scalars[SC_RZ_NEXT] = rz; P.scalars[SC_RZ0] = rz0;
+        P.flags[FL_PCG_ITERS] = it; P.flags[FL_PCG_ITERS_NEXT] = it;
+        if (G > 1) *P.xchg_ctr = seq;
+        P.ps_clock[0] = (double)t_m; P.ps_clock[1] = (double)t_s1; P.ps_clock[2] = (double)t_f; P.ps_clock[3] = (double)t_s2;
+    }
+}
+
+static int ps_grid_blocks() {
+    static int blocks = -1;
+    if (blocks < 0) {
+        int dev = 0, coop = 0, sms = 0, per_sm = 0, smem_max = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        blocks = 0;
+        if (coop && smem_max >= (int)sizeof(PsSmem) &&
+            cudaFuncSetAttribute(k_pcg_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsSmem)) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve, PS_THREADS, sizeof(PsSmem)) == cudaSuccess && per_sm >= 1)
+            blocks = sms;
+        cudaGetLastError();
+    }
+    return blocks;
+}
+int pcg_solve_grid() { return ps_grid_blocks(); }
+int pcg_solve_items(int n_cams) { return (6 * n_cams + PS_ITEM - 1) / PS_ITEM; }
+int pcg_solve_slot() { return PS_SLOT; }
+bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStream_t st) {
+    if (!P.ps_on || P.ps_grid != ps_grid_blocks()) return false;
+    DevProblem Pc = P;
+    void* args[] = {&Pc, &tol2, &max_iters};
+    return cudaLaunchCooperativeKernel((void*)k_pcg_solve, dim3(P.ps_grid), dim3(PS_THREADS), args, sizeof(PsSmem), st) == cudaSuccess;
+}
+
+}  // namespace sba
