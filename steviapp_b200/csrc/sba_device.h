@@ -107,8 +107,10 @@ struct DevProblem {
     //   uint32_t flag[2][xchg_n][xchg_nflag]      (= exchange number once the source rank's block has pushed its slice)
     int32_t xchg_n;       // ranks (0 = exchange through NCCL instead)
     int32_t xchg_rank;
-    int32_t xchg_stride;  // doubles per (parity, source) buffer: max(pcg_blocks * 192, ps_nitems * 128)
-    int32_t xchg_nflag;   // flags per (parity, source): max(pcg_blocks, ps_nitems)
+    int32_t xchg_stride;  // doubles per (parity, source) buffer = pcg_blocks * 192
+    int64_t xchg_ll_off;  // doubles from the mailbox base to the low-latency region of the persistent PCG kernel:
+                          //   uint4 ll[2][xchg_n][ps_nitems][128] = {lo, seq, hi, seq} per value (flag travels with the data)
+    int32_t xchg_nflag;   // flags per (parity, source) = pcg_blocks
     double* xchg_peer[8]; // mailbox base of every rank (own entry = local pointer)
     uint32_t* xchg_ctr;   // local: number of exchanges completed so far (identical on every rank)
     // ---- persistent PCG kernel (sba_kernels_pcgsolve.cu): static schedule of the tile mat-vec and of the fold ----
@@ -213,7 +215,8 @@ int pcg_solve_slot();                                                   // mailb
 bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // whole PCG solve, one cooperative launch
 int pcg_xchg_nflag(const DevProblem& P);
 int pcg_xchg_stride(const DevProblem& P);                               // doubles per (parity, source) mailbox buffer
-size_t pcg_xchg_bytes(const DevProblem& P, int nranks);                 // mailbox size
+size_t pcg_xchg_bytes(const DevProblem& P, int nranks);                 // mailbox size of the fused-kernel exchange (data + flags)
+size_t pcg_xchg_ll_bytes(const DevProblem& P, int nranks);              // + low-latency region of the persistent kernel
 void launch_pcg_A(const DevProblem& P, int mode, cudaStream_t st);    // q (from tile partials or all-reduced) + p.q partials
 void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t st);   // alpha, x, r, z | beta, p (frozen once converged)
 void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st);   // operator pass 2, tile partials only

@@ -262,8 +262,9 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_ABC(DevProblem P, int mode, d
 }
 
 int pcg_blocks(const DevProblem& P) { return cdiv(6 * P.Nc, PCG_BLOCK); }
-int pcg_xchg_nflag(const DevProblem& P) { return std::max(pcg_blocks(P), pcg_solve_items(P.Nc)); }
-int pcg_xchg_stride(const DevProblem& P) { return std::max(pcg_blocks(P) * PCG_BLOCK, pcg_solve_items(P.Nc) * pcg_solve_slot()); }
+int pcg_xchg_nflag(const DevProblem& P) { return pcg_blocks(P); }
+int pcg_xchg_stride(const DevProblem& P) { return pcg_blocks(P) * PCG_BLOCK; }
+size_t pcg_xchg_ll_bytes(const DevProblem& P, int nranks) { return 2 * (size_t)nranks * pcg_solve_items(P.Nc) * pcg_solve_slot() * 16; }
 size_t pcg_xchg_bytes(const DevProblem& P, int nranks) {
     return 2 * (size_t)nranks * pcg_xchg_stride(P) * sizeof(double) + 2 * (size_t)nranks * pcg_xchg_nflag(P) * sizeof(uint32_t);
 }

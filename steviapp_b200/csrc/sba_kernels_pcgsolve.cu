@@ -300,32 +300,36 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
             double pq = ps_fold(P.ps_pq, gridDim.x, sm.sh);   // this rank's p^T S p / 2 (barriers inside: sm.v is visible below)
             double q_i = 0.0;
             if (tid < PS_ITEM) q_i = (sm.v[0][tid] + sm.v[1][tid]) + sm.v[2][tid];
-            if (G > 1) {   // sum q and p.q over the ranks, rank order, through the peer mailboxes
+            if (G > 1) {
+                // sum q and p.q over the ranks, in rank order, through the peer mailboxes -- low-latency protocol: every 8-byte
+                // value travels as ONE 16-byte store {lo, seq, hi, seq}, so the flag arrives with the data (each 8-byte half
+                // validates itself) and no fence / second round trip is needed: one NVLink write latency per exchange.
+                // Slots alternate with the parity of seq (a rank is at most one exchange ahead of a peer).
                 seq++;
-                const int par = (int)(seq & 1u);
-                const size_t stride = (size_t)P.xchg_stride;
-                const double mine = tid < PS_ITEM ? q_i : pq;
                 if (tid <= PS_ITEM) {
+                    const double mine = tid < PS_ITEM ? q_i : pq;
+                    const unsigned long long bits = (unsigned long long)__double_as_longlong(mine);
+                    const uint32_t lo = (uint32_t)bits, hi = (uint32_t)(bits >> 32);
+                    const size_t slot = ((size_t)((seq & 1u) * G) * P.ps_nitems + b) * PS_SLOT + tid;   // + source * nitems * PS_SLOT
+                    const size_t src_stride = (size_t)P.ps_nitems * PS_SLOT;
                     for (int g = 0; g < G; g++)
-                        if (g != me) __stcg(P.xchg_peer[g] + (size_t)(par * G + me) * stride + (size_t)b * PS_SLOT + tid, mine);
-                }
-                __threadfence_system();
-                __syncthreads();
-                if (tid < G && tid != me) {
-                    const int g = tid;
-                    uint32_t* fl_g = reinterpret_cast<uint32_t*>(P.xchg_peer[g] + 2 * (size_t)G * stride);
-                    const uint32_t* fl_me = reinterpret_cast<const uint32_t*>(P.xchg_peer[me] + 2 * (size_t)G * stride);
-                    ps_st_release_sys(fl_g + (size_t)(par * G + me) * P.xchg_nflag + b, seq);
-                    const uint32_t* w = fl_me + (size_t)(par * G + g) * P.xchg_nflag + b;
-                    const long long t0 = clock64();
-                    while (ps_ld_acquire_sys(w) != seq)
-                        if (clock64() - t0 > 6000000000LL) { P.flags[FL_XCHG_TIMEOUT] = 1; break; }   // ~3 s: a peer died
-                }
-                __syncthreads();
-                if (tid <= PS_ITEM) {
+                        if (g != me) {
+                            uint4* dst = reinterpret_cast<uint4*>(P.xchg_peer[g] + P.xchg_ll_off) + slot + (size_t)me * src_stride;
+                            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst), "r"(lo), "r"(seq), "r"(hi), "r"(seq) : "memory");
+                        }
                     double acc = 0.0;
-                    for (int g = 0; g < G; g++)
-                        acc += g == me ? mine : __ldcg(P.xchg_peer[me] + (size_t)(par * G + g) * stride + (size_t)b * PS_SLOT + tid);
+                    const long long t0 = clock64();
+                    for (int g = 0; g < G; g++) {
+                        if (g == me) { acc += mine; continue; }
+                        const uint4* srcp = reinterpret_cast<const uint4*>(P.xchg_peer[me] + P.xchg_ll_off) + slot + (size_t)g * src_stride;
+                        uint32_t a0, f0, a1, f1;
+                        while (true) {
+                            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a0), "=r"(f0), "=r"(a1), "=r"(f1) : "l"(srcp) : "memory");
+                            if (f0 == seq && f1 == seq) break;
+                            if (clock64() - t0 > 6000000000LL) { P.flags[FL_XCHG_TIMEOUT] = 1; break; }   // ~3 s: a peer died
+                        }
+                        acc += __longlong_as_double((long long)(((unsigned long long)a1 << 32) | a0));
+                    }
                     if (tid < PS_ITEM) q_i = acc; else sm.pq = acc;
                 }
                 __syncthreads();
