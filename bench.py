@@ -149,9 +149,9 @@ def bench_config(a):
     return {"workload": f"synthetic {a.shape}-shape BA: {nc} cameras / {npt} points / {no} observations, plane cost, "
                         "intrinsics constant, first camera fixed, 4 GCP priors",
             "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
-            "linear_solver": "Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; "
-                             "multi-GPU: partial tiles reduce-scattered, every rank applies its slice, the 6*Nc partial is all-reduced inside "
-                             "the fused PCG kernel over NVLink peer mailboxes)",
+            "linear_solver": "Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration); "
+                             "whole PCG solve = one persistent cooperative kernel (TMA bulk-copy ring); multi-GPU: partial tiles reduce-scattered, "
+                             "every rank applies its slice, the 6*Nc partial is all-reduced inside that kernel over NVLink peer mailboxes",
             "step": "one LM iteration, fixed count (tolerances 0), every run restarts from the same initial values",
             "l2": "working set ~1.2 GB per evaluation >> 126 MB L2 (no flush needed)",
             "parallelism": f"points sharded over {a.gpus} GPU(s), cameras replicated"}
@@ -286,12 +286,27 @@ def run_b200(a):
                                   "contributions": ex["n_contributions"], "blocks": ex["n_blocks"]}
         share = {"k_explicit_matvec": pcg_per_step * kern["k_explicit_matvec"]["ms"], "explicit_build": kern["explicit_build"]["ms"],
                  "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
+        if shard["persistent_pcg"]:
+            # the PCG of an LM iteration is ONE launch of the persistent kernel k_pcg_solve (mat-vec, folds, exchange and vector
+            # updates of every CG iteration): duration = the PCG phase of the TIMED region above (CUDA events on the solver's
+            # stream around that single launch), algorithmic bytes = one read of this rank's tiles per CG iteration
+            ms = r["ms_pcg"] / a.steps
+            nbytes = pcg_per_step * shard["n_own"] * TILE_BYTES
+            kern["k_pcg_solve"] = {"ms": ms, "GBps": nbytes / (ms * 1e-3) / 1e9, "alg_bytes_per_launch": nbytes,
+                                   "cg_iterations_per_launch": pcg_per_step, "us_per_cg_iteration": ms * 1e3 / max(pcg_per_step, 1),
+                                   "alg_bytes_per_cg_iteration": shard["n_own"] * TILE_BYTES, "tiles": shard["n_own"],
+                                   "note": ("slice of the tiles < 126 MB L2: re-read from L2 after the first CG iteration, the HBM roofline does not bound it"
+                                            if shard["n_own"] * TILE_BYTES < 120e6 else "tiles streamed from HBM every CG iteration")}
+            kern["k_explicit_matvec"]["note"] = "stand-alone tile mat-vec kernel (operator hook / fallback), not launched by the PCG"
+            share = {"k_pcg_solve": ms, "explicit_build": kern["explicit_build"]["ms"], "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
     else:
         share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
     dom = max(share, key=share.get)
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        if isinstance(traffic, dict):   # persistent kernel: ncu measured one launch of 114 CG iterations; per launch of THIS run
+            traffic = traffic["bytes_per_cg_iteration"] * pcg_per_step * (shard["n_own"] / max(ex["n_tiles"], 1))
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",

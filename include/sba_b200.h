@@ -237,8 +237,10 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles,
 /* multi-GPU view of the explicit system: the summed tiles are sharded in contiguous ranges (one reduce-scatter per LM
  * iteration); this rank applies the tiles first_tile .. first_tile + n_own - 1.  peer_exchange = 1 when the per-iteration
  * all-reduce of the 6 n_cams operator partial runs inside the fused PCG kernel over CUDA-IPC peer mailboxes (NVLink),
- * 0 when it goes through NCCL (or on one GPU).  Measurement only; no reference counterpart. */
-int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange);
+ * 0 when it goes through NCCL (or on one GPU).  persistent_pcg = 1 when the whole PCG solve of an LM iteration runs as
+ * one persistent cooperative kernel (k_pcg_solve).  Measurement only; no reference counterpart. */
+int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange,
+                       int32_t* persistent_pcg);
 
 /* inspection hook: copies the tiles of the explicit reduced camera system as last built (n_tiles * 384 * 384 doubles,
  * row-major tiles; tile t covers camera tiles (tile_i[t], tile_j[t]), i <= j; diagonal tiles hold S_ii / 2 on their

@@ -106,7 +106,7 @@ def load():
     lib.sba_partition_points.argtypes = [i32, vp, i32, vp]
     lib.sba_problem_sizes.argtypes = [vp, P(i32), P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_info.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
-    lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32)]
+    lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

@@ -122,11 +122,12 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles, i
     return SBA_OK;
 }
 
-int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange) {
+int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange, int32_t* persistent_pcg) {
     GUARD(s);
     const sba::DevProblem& P = s->impl.P;
     if (first_tile) *first_tile = P.ex_on ? P.ex_own0 : 0; if (n_own) *n_own = P.ex_on ? P.ex_nown : 0;
     if (peer_exchange) *peer_exchange = P.xchg_n > 0 ? 1 : 0;
+    if (persistent_pcg) *persistent_pcg = (P.ex_on && P.ps_on) ? 1 : 0;
     return SBA_OK;
 }
 

@@ -26,6 +26,7 @@ Solver::Solver(const sba_options& o) : opt(o) {}
 Solver::~Solver() {
     if (st) cudaStreamSynchronize(st);
     release_peer_exchange();
+    unpin_all();
     comm.destroy();
     timer.destroy();
     arena.release();
@@ -108,6 +109,7 @@ int Solver::set_poses(double* raxis, double* t, int32_t n, const int32_t* model,
                       const uint8_t* kind) {
     if (n <= 0 || !raxis || !t) return fail(SBA_ERR_INVALID, "set_poses: null arrays or n <= 0");
     if (finalized && n != Nc) return fail(SBA_ERR_INVALID, "set_poses: pose count changed after finalize");
+    if (raxis != h_raxis || t != h_t) unpin_all();
     h_raxis = raxis; h_t = t; Nc = n;
     if (!finalized) {
         cam_model.assign(n, 0); cam_fixed.assign(n, 0); cam_kind.assign(n, 0);
@@ -121,6 +123,7 @@ int Solver::set_poses(double* raxis, double* t, int32_t n, const int32_t* model,
 int Solver::set_points(double* xyz, int32_t n, const uint8_t* fixed) {
     if (n < 0 || (n > 0 && !xyz)) return fail(SBA_ERR_INVALID, "set_points: null array");
     if (finalized && n != Np) return fail(SBA_ERR_INVALID, "set_points: point count changed after finalize");
+    if (xyz != h_xyz) unpin_all();
     h_xyz = xyz; Np = n;
     if (!finalized) {
         pt_fixed.assign(n, 0);

@@ -133,6 +133,10 @@ private:
     void* xchg_mailbox = nullptr;  // this rank's mailbox of the peer-memory all-reduce (own cudaMalloc: exported through CUDA IPC)
     std::vector<void*> ipc_opened; // peer mailboxes opened with cudaIpcOpenMemHandle
     void release_peer_exchange();
+    struct Pinned { const void* p; size_t bytes; bool ok; };
+    std::vector<Pinned> pinned;    // caller parameter arrays registered with cudaHostRegister (sba_solver_layout.inc)
+    bool pin_caller(const void* p, size_t bytes);
+    void unpin_all();
 };
 
 }  // namespace sba

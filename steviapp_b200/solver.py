@@ -194,9 +194,9 @@ class SBASolver:
 
     def explicit_shard(self):
         """This rank's slice of the explicit system's tiles and whether the PCG all-reduce runs over peer mailboxes."""
-        v = [C.c_int32() for _ in range(3)]
+        v = [C.c_int32() for _ in range(4)]
         self._check(self._lib.sba_explicit_shard(self._h, *[C.byref(x) for x in v]))
-        return dict(zip(("first_tile", "n_own", "peer_exchange"), [x.value for x in v]))
+        return dict(zip(("first_tile", "n_own", "peer_exchange", "persistent_pcg"), [x.value for x in v]))
 
     def explicit_dense(self):
         """The reduced camera system of the last LM iteration as a dense symmetric matrix (6 n_cams)^2 and its rhs
