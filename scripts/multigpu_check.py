@@ -15,6 +15,7 @@ from steviapp_b200 import SBASolver, synthetic, comm_unique_id
 
 shape = sys.argv[1] if len(sys.argv) > 1 else "ladybug"
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -32,6 +33,8 @@ if rank == 0:
 results = []
 all_ok = True
 for name, op_mode, peer in (("explicit+peer", 3, "1"), ("explicit+nccl", 3, "0"), ("implicit+peer", 2, "1"), ("implicit+nccl", 2, "0")):
+    if only and name not in only:
+        continue
     os.environ["SBA_PEER_XCHG"] = peer
     s = SBASolver(device=local, pcg_check_every=4, operator_mode=op_mode, **fixed)
     uid = [comm_unique_id() if rank == 0 else None]
