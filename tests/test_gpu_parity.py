@@ -352,3 +352,31 @@ def test_two_gpu_sharded_solve_matches_single_gpu():
     res = json.loads(line)
     assert res["ok"] and {m["mode"] for m in res["modes"]} == {"explicit+peer", "explicit+nccl", "implicit+peer", "implicit+nccl"}
     assert res["modes"][0]["info"][0]["peer_exchange"] == 1 and res["modes"][0]["info"][0]["persistent_pcg"] == 1
+
+
+def test_venice_scale_explicit_tiles_against_implicit_operator(monkeypatch):
+    """Full BASELINE size: the explicit reduced camera system (406 dense tiles built from 11.6 M point-pair contributions) and
+    the implicit operator (two passes over the 5 M observations) are independent code paths for the same S; they must agree
+    on S x and on the reduced right-hand side.  Then the persistent PCG kernel against the two-kernel path on those tiles."""
+    sc = synthetic.make_scene("venice")
+    rng = np.random.default_rng(7)
+    lam_c = rng.uniform(0.5, 2.0, (sc["n_cams"], 6)); lam_p = rng.uniform(0.5, 2.0, (sc["n_pts"], 3))
+    x = rng.normal(size=(sc["n_cams"], 6))
+    res = {}
+    for mode in (2, 3):
+        s, _ = gpu_solver(sc, operator_mode=mode)
+        res[mode] = s.schur_matvec(lam_c, lam_p, x)
+        if mode == 3:
+            info = s.explicit_info()
+            assert info["enabled"] and info["n_tiles"] == 406
+        s.close()
+    assert relerr(res[3][0], res[2][0]) < 1e-11 and relerr(res[3][1], res[2][1]) < 1e-11
+    out = {}
+    for persistent in ("1", "0"):
+        monkeypatch.setenv("SBA_PCG_PERSISTENT", persistent)
+        s, _ = gpu_solver(sc, pcg_check_every=8)
+        out[persistent] = s.solve(max_iterations=2, **FIXED_ITERS)
+        s.close()
+    for a, b in zip(out["1"]["cost_history"], out["0"]["cost_history"]):
+        assert abs(a - b) <= 1e-11 * b
+    assert all(abs(a - b) <= 1 for a, b in zip(out["1"]["pcg_iters_history"], out["0"]["pcg_iters_history"]))
