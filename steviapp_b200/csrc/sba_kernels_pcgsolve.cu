@@ -27,6 +27,7 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "sba_kernel_util.cuh"
 
@@ -79,6 +80,12 @@ __device__ __forceinline__ void ps_bulk_load(void* dst, const void* src, uint32_
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  :: "r"(ps_saddr(dst)), "l"(src), "r"(bytes), "r"(ps_saddr(bar)) : "memory");
 }
+// same with an L2 eviction-priority hint (createpolicy): evict_last for the part of the run that is to stay L2-resident
+// across the CG iterations, evict_first for the part that only streams through
+__device__ __forceinline__ void ps_bulk_load_hint(void* dst, const void* src, uint32_t bytes, unsigned long long* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(ps_saddr(dst)), "l"(src), "r"(bytes), "r"(ps_saddr(bar)), "l"(policy) : "memory");
+}
 __device__ __forceinline__ void ps_consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(32 * PS_CWARPS) : "memory"); }
 
 __device__ __forceinline__ uint32_t ps_ld_acquire_sys(const uint32_t* p) {
@@ -113,7 +120,7 @@ __device__ __forceinline__ double ps_warp_sum8(const double (&v)[8], int lane) {
     return q;   // total of value (lane >> 2) in every lane
 }
 
-__global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters) {
+__global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters, int pin_hg) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char ps_smem_raw[];
     PsSmem& sm = *reinterpret_cast<PsSmem*>(ps_smem_raw);
@@ -191,11 +198,18 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         // ---- M: tile mat-vec over this CTA's run
         if (producer) {
             if (lane == 0) {
+                // the first pin_hg half groups of every run are loaded evict_last: S does not change during the solve, so that
+                // share of the tiles (sized to the L2 by the host) is served from L2 from the second CG iteration on; the rest
+                // streams through evict_first and cannot push it out
+                uint64_t pol_keep, pol_stream;
+                asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+                asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
                 for (unsigned int h = 0; h < 2u * ng; h++) {
                     const unsigned int H = 2u * jdone + h, s = H % PS_STAGES, use = H / PS_STAGES;
                     if (use > 0) ps_mbar_wait(&sm.empty[s], (use - 1) & 1u);   // the owner warp has released the previous contents
                     ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
-                    ps_bulk_load(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s]);
+                    ps_bulk_load_hint(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s],
+                                      (int)h < pin_hg ? pol_keep : pol_stream);
                 }
             }
         } else {
@@ -384,7 +398,11 @@ int pcg_solve_slot() { return PS_SLOT; }
 bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStream_t st) {
     if (!P.ps_on || P.ps_grid != ps_grid_blocks()) return false;
     DevProblem Pc = P;
-    void* args[] = {&Pc, &tol2, &max_iters};
+    // share of the rank's tiles kept L2-resident across the CG iterations (SBA_PS_L2_MB, default 80 MB of the 126 MB L2),
+    // as the same number of leading 12 KB half groups of every CTA's run
+    static const double l2_mb = std::getenv("SBA_PS_L2_MB") ? std::atof(std::getenv("SBA_PS_L2_MB")) : 80.0;
+    int pin_hg = (int)(l2_mb * 1e6 / ((double)P.ps_grid * PS_STAGE_BYTES));
+    void* args[] = {&Pc, &tol2, &max_iters, &pin_hg};
     return cudaLaunchCooperativeKernel((void*)k_pcg_solve, dim3(P.ps_grid), dim3(PS_THREADS), args, sizeof(PsSmem), st) == cudaSuccess;
 }
 
