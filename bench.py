@@ -296,7 +296,8 @@ def run_b200(a):
                                    "cg_iterations_per_launch": pcg_per_step, "us_per_cg_iteration": ms * 1e3 / max(pcg_per_step, 1),
                                    "alg_bytes_per_cg_iteration": shard["n_own"] * TILE_BYTES, "tiles": shard["n_own"],
                                    "note": ("slice of the tiles < 126 MB L2: re-read from L2 after the first CG iteration, the HBM roofline does not bound it"
-                                            if shard["n_own"] * TILE_BYTES < 120e6 else "tiles streamed from HBM every CG iteration")}
+                                            if shard["n_own"] * TILE_BYTES < 120e6 else "tiles streamed from HBM every CG iteration; the leading 80 MB are loaded evict_last and re-read from L2, so the "
+                                                 "algorithmic rate can exceed the HBM peak (roofline.traffic = DRAM bytes measured by ncu)")}
             kern["k_explicit_matvec"]["note"] = "stand-alone tile mat-vec kernel (operator hook / fallback), not launched by the PCG"
             share = {"k_pcg_solve": ms, "explicit_build": kern["explicit_build"]["ms"], "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
     else:
