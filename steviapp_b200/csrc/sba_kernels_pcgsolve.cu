@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     }
     unsigned int jdone = 0;   // groups streamed in the previous iterations: stage = (2 * group number + half) % 16
     // phase clock of CTA 0 (ns, summed over the iterations): mat-vec, barrier 1, fold + vector part, barrier 2 + scalars
-    auto now = [&]() -> long long { long long t = 0; if (b == 0 && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
+    auto now = [&]() -> long long { long long t = 0; if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
     long long t_m = 0, t_s1 = 0, t_f = 0, t_s2 = 0, t_a = now();
 
     while (rz > tol2 * rz0 && rz0 > 0.0 && it < max_iters) {
@@ -372,6 +372,11 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         P.flags[FL_PCG_ITERS] = it; P.flags[FL_PCG_ITERS_NEXT] = it;
         if (G > 1) *P.xchg_ctr = seq;
         P.ps_clock[0] = (double)t_m; P.ps_clock[1] = (double)t_s1; P.ps_clock[2] = (double)t_f; P.ps_clock[3] = (double)t_s2;
+    }
+    if (tid == 0) {   // per-CTA mat-vec time and SM (measurement only)
+        unsigned int smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        P.ps_clock[4 + 2 * b] = (double)t_m; P.ps_clock[5 + 2 * b] = (double)smid;
     }
 }
 
