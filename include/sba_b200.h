@@ -179,6 +179,14 @@ int sba_evaluate(sba_solver* s, double* cost, double* residuals,
 /* Test hooks on the linear algebra (same shapes as the oracle's):
  * gc 6*n_cams, gp 3*n_pts, Hcc 36*n_cams, Hpp 9*n_pts (undamped). */
 int sba_normal_blocks(sba_solver* s, double* gc, double* gp, double* Hcc, double* Hpp);
+/* Jacobian of the residuals with respect to the five intrinsic blocks f[1], pp[2], k[3], t[2], B[2] of each observation's
+ * camera model, n_obs x 2 x 10 row-major, caller order, at the current parameters: the blocks the reference's
+ * AutoDiffCostFunction<..., 2, 3,3,3, 1,2,3,2,2> (sbamodules/pinholecameraprojectormodule.cpp:105-122) differentiates when
+ * the intrinsics are free (PinholeCamProjModule::init, :302-533).  The B columns are identically zero (the skew is built
+ * from the tangential block, pinholecameraprojectormodule.h:46-47).  First half of SURVEY 8(f) row 1: the LM itself still
+ * holds the intrinsics constant (FixedParameter::CameraInternal). */
+int sba_evaluate_intrinsics_jacobian(sba_solver* s, double* jac_intr);
+
 /* y = S x and reduced rhs for explicit damping diagonals lam_c (6*n_cams), lam_p (3*n_pts) */
 int sba_schur_matvec(sba_solver* s, const double* lam_c, const double* lam_p,
                      const double* x, double* y, double* rhs);

@@ -96,6 +96,13 @@ class Problem:
         rc = lib.oracle_evaluate(C.byref(self.c), threads, C.byref(cost), _p(r), _p(jc), _p(jp), _p(failed))
         return {"cost": cost.value, "ok": rc == 0, "residuals": r, "jac_cam": jc, "jac_pt": jp, "failed": failed}
 
+    def intrinsics_jac(self):
+        """d res / d (f, pp, k, t, B) per observation (n_obs, 2, 10): autodiff of the reference functor over the five intrinsic blocks."""
+        lib = load()
+        j = np.empty((self.n_obs, 2, 10))
+        lib.oracle_evaluate_intrinsics_jac(C.byref(self.c), _p(j))
+        return j
+
     def normal_blocks(self, threads=0):
         lib = load()
         gc = np.empty((self.n_cams, 6)); gp = np.empty((self.n_pts, 3))

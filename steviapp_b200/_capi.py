@@ -22,7 +22,7 @@ EXPORTS = [
     "sba_default_options", "sba_create", "sba_destroy", "sba_last_error", "sba_create_error",
     "sba_set_intrinsics", "sba_set_poses", "sba_set_points", "sba_add_observations", "sba_add_priors",
     "sba_finalize", "sba_upload_parameters", "sba_download_parameters", "sba_evaluate",
-    "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
+    "sba_evaluate_intrinsics_jacobian", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_tiles", "sba_version",
 ]
@@ -106,6 +106,7 @@ def load():
     lib.sba_partition_points.argtypes = [i32, vp, i32, vp]
     lib.sba_problem_sizes.argtypes = [vp, P(i32), P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_info.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
+    lib.sba_evaluate_intrinsics_jacobian.argtypes = [vp, vp]
     lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
     for name in EXPORTS:

@@ -82,6 +82,8 @@ int sba_triangulate(sba_solver* s, int32_t n_points, const int32_t* view_off, co
                     double* xyz_out, uint8_t* ok_out, double* ms_kernel) {
     GUARD(s); return s->impl.triangulate(n_points, view_off, view_cam, view_uv, xyz_out, ok_out, ms_kernel);
 }
+int sba_evaluate_intrinsics_jacobian(sba_solver* s, double* jac_intr) { GUARD(s); return s->impl.evaluate_intrinsics_jacobian(jac_intr); }
+
 int sba_comm_unique_id(uint8_t id128[128]) {
     std::string err;
     if (sba::Comm::unique_id(id128, err)) { g_create_error = err; return SBA_ERR_COMM; }

@@ -79,6 +79,30 @@ void launch_gather_outputs(const DevProblem& P, const int32_t* slot_of_obs, doub
     k_gather_outputs<<<cdiv(P.No, 256), 256, 0, st>>>(P, slot_of_obs, res_out, jc_out, jp_out);
 }
 
+// intrinsics Jacobian hook: d res / d (f, pp, k, t, B), 2 x 10 per observation, caller order.
+// Thread per observation; the camera of a slot is found by bisection of the tile starts (slots are camera-sorted).
+__global__ void __launch_bounds__(128) k_intrinsics_jacobian(DevProblem P, const int32_t* __restrict__ slot_of_obs, double* jac_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.No) return;
+    const int s = slot_of_obs[i];
+    int lo = 0, hi = P.Nt - 1;
+    while (lo < hi) {   // last tile with tile_start <= s
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(P.tile_start + mid) <= s) lo = mid; else hi = mid - 1;
+    }
+    const int cam = __ldg(P.tile_cam + lo), pt = P.obs_pt[s];
+    const size_t Ns = (size_t)P.Ns;
+    double W[4];
+    if (P.obs_info) for (int k = 0; k < 4; k++) W[k] = P.obs_info[(size_t)k * Ns + s];
+    double J[20];
+    obs_intr_jac(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam, P.pts + 4 * (size_t)pt, P.obs_uv[2 * (size_t)s], P.obs_uv[2 * (size_t)s + 1],
+                 P.intr + 10 * P.cam_model[cam], P.obs_info ? W : nullptr, P.cam_kind[cam], J);
+    for (int k = 0; k < 20; k++) jac_out[20 * (size_t)i + k] = J[k];
+}
+void launch_intrinsics_jacobian(const DevProblem& P, const int32_t* slot_of_obs, double* jac_out, cudaStream_t st) {
+    if (P.No) k_intrinsics_jacobian<<<cdiv(P.No, 128), 128, 0, st>>>(P, slot_of_obs, jac_out);
+}
+
 __global__ void k_pack_points(const double* __restrict__ xyz3, double* pts4, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;

@@ -185,6 +185,72 @@ SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const d
     return true;
 }
 
+// d res / d (f, pp[2], k[3], t[2], B[2]) of one observation, 2 x 10 row-major -- the Jacobian blocks the reference's
+// AutoDiffCostFunction<..., 2, 3,3,3, 1,2,3,2,2> produces for the five intrinsic blocks when they are free
+// (sbamodules/pinholecameraprojectormodule.cpp:105-122,302-533).  Closed form:
+//   res = W e(Pbar, d),  d = dirFromUV(uv; intr)  ->  d res / d intr = W (d e / d d) (d d / d intr);
+// the B columns are identically zero (the skew is built from the tangential block, pinholecameraprojectormodule.h:46-47).
+// Returns false (and zeros) when the plane cost fails (Pbar.z < 0).
+SBA_HD bool obs_intr_jac(const double* cc, const double* X, double u, double v, const double* in, const double* W,
+                         int spherical, double* J) {
+    for (int k = 0; k < 20; k++) J[k] = 0.0;
+    // ---- d and d d / d intr (3 x 8; d_z = f)
+    const double f = in[0], t1 = in[6], t2 = in[7];
+    const double y = (v - in[2]) / f;
+    const double D = f + t1;
+    const double x = (u - in[1] - t2 * y) / D;
+    const double r2 = x * x + y * y;
+    const double rad = r2 * (in[3] + r2 * (in[4] + r2 * in[5]));
+    const double Rp = in[3] + r2 * (2.0 * in[4] + 3.0 * r2 * in[5]);   // d rad / d r2
+    const double xy = x * y;
+    const double g0 = x + x * rad + 2.0 * xy * t1 + (r2 + 2.0 * x * x) * t2;
+    const double g1 = y + y * rad + (r2 + 2.0 * y * y) * t1 + 2.0 * xy * t2;
+    const double g0x = 1.0 + rad + 2.0 * x * x * Rp + 2.0 * y * t1 + 6.0 * x * t2, g0y = 2.0 * xy * Rp + 2.0 * x * t1 + 2.0 * y * t2;
+    const double g1x = g0y, g1y = 1.0 + rad + 2.0 * y * y * Rp + 6.0 * y * t1 + 2.0 * x * t2;
+    // x, y as functions of (f, ppx, ppy, t1, t2): columns 0, 1, 2, 6, 7
+    const double y_f = -y / f, y_py = -1.0 / f;
+    const double x_f = (t2 * y / f - x) / D, x_px = -1.0 / D, x_py = t2 / (f * D), x_t1 = -x / D, x_t2 = -y / D;
+    double dd0[8], dd1[8];   // d d_x / d intr[c], d d_y / d intr[c], c = f, ppx, ppy, k1, k2, k3, t1, t2
+    dd0[0] = g0 + f * (g0x * x_f + g0y * y_f); dd1[0] = g1 + f * (g1x * x_f + g1y * y_f);
+    dd0[1] = f * g0x * x_px;                   dd1[1] = f * g1x * x_px;
+    dd0[2] = f * (g0x * x_py + g0y * y_py);    dd1[2] = f * (g1x * x_py + g1y * y_py);
+    dd0[3] = f * x * r2;                       dd1[3] = f * y * r2;
+    dd0[4] = f * x * r2 * r2;                  dd1[4] = f * y * r2 * r2;
+    dd0[5] = f * x * r2 * r2 * r2;             dd1[5] = f * y * r2 * r2 * r2;
+    dd0[6] = f * (2.0 * xy + g0x * x_t1);              dd1[6] = f * (r2 + 2.0 * y * y + g1x * x_t1);
+    dd0[7] = f * (r2 + 2.0 * x * x + g0x * x_t2);      dd1[7] = f * (2.0 * xy + g1x * x_t2);
+    const double d0 = g0 * f, d1 = g1 * f, d2 = f;
+    // ---- d e / d d (2 x 3): rows (ex0, 0, ex2), (0, ey1, ey2)
+    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
+    const double Px = cc[0] * vx + cc[1] * vy + cc[2] * vz;
+    const double Py = cc[3] * vx + cc[4] * vy + cc[5] * vz;
+    const double Pz = cc[6] * vx + cc[7] * vy + cc[8] * vz;
+    double ex0, ex2, ey1, ey2;
+    if (!spherical) {
+        if (Pz < 0.0) return false;
+        ex0 = -1.0; ey1 = -1.0; ex2 = Px / Pz; ey2 = Py / Pz;      // e = d_z Pbar_xy / Pbar_z - d_xy
+    } else {
+        // e_a = theta_a s_a, theta_a = atan2(Pbar_a, Pbar_z) - atan2(d_a, d_z) (as the rotated pair of obs_eval), s_a = (d_a^2 + d_z^2) / d_z:
+        // d e_a / d d_a = -1 + 2 theta_a d_a / d_z,  d e_a / d d_z = d_a / d_z + theta_a (1 - d_a^2 / d_z^2)
+        const double nx2 = d0 * d0 + d2 * d2, ny2 = d1 * d1 + d2 * d2;
+        const double inx = 1.0 / sqrt(nx2), iny = 1.0 / sqrt(ny2);
+        const double cx = d2 * inx, sx = d0 * inx, cy = d2 * iny, sy = d1 * iny;
+        const double thx = atan2(cx * Px - sx * Pz, cx * Pz + sx * Px), thy = atan2(cy * Py - sy * Pz, cy * Pz + sy * Py);
+        const double ax = d0 / d2, ay = d1 / d2;
+        ex0 = -1.0 + 2.0 * thx * ax; ex2 = ax + thx * (1.0 - ax * ax);
+        ey1 = -1.0 + 2.0 * thy * ay; ey2 = ay + thy * (1.0 - ay * ay);
+    }
+    double E0[8], E1[8];
+    for (int c = 0; c < 8; c++) { E0[c] = ex0 * dd0[c]; E1[c] = ey1 * dd1[c]; }
+    E0[0] += ex2; E1[0] += ey2;   // d d_z / d f = 1
+    for (int c = 0; c < 8; c++) {
+        J[c] = W ? W[0] * E0[c] + W[1] * E1[c] : E0[c];
+        J[10 + c] = W ? W[2] * E0[c] + W[3] * E1[c] : E1[c];
+    }
+    return true;
+}
+
+
 // Pi = d e / d Pbar rebuilt from Pbar and the aux scale constants (identity stiffness):
 // rows (p00, 0, p02), (0, p11, p12).  Same expressions as in obs_eval.
 SBA_HD void pi_from_pbar(double Px, double Py, double Pz, double kx, double ky, int spherical,

@@ -186,6 +186,13 @@ class SBASolver:
         self._check(self._lib.sba_problem_sizes(self._h, *[C.byref(x) for x in v]))
         return dict(zip(("n_cams", "n_pts", "n_obs", "n_slots", "n_tiles"), [x.value for x in v]))
 
+    def intrinsics_jacobian(self):
+        """d res / d (f, pp[2], k[3], t[2], B[2]) per observation, (n_obs, 2, 10), caller order, at the current parameters."""
+        self.finalize()
+        j = np.empty((self.sizes()["n_obs"], 2, 10))
+        self._check(self._lib.sba_evaluate_intrinsics_jacobian(self._h, _ptr(j)))
+        return j
+
     def explicit_info(self):
         """Static sizes of the explicit reduced camera system (enabled = the PCG applies S from the tiles)."""
         v = [C.c_int32() for _ in range(4)]

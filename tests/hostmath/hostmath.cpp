@@ -28,6 +28,20 @@ int hm_evaluate(int32_t n_obs, const int32_t* cam, const int32_t* pt, const doub
     return bad;
 }
 
+// intrinsics Jacobian (2 x 10 per observation), SURVEY 8(f) row 1
+int hm_intrinsics_jac(int32_t n_obs, const int32_t* cam, const int32_t* pt, const double* cam_r, const double* cam_t,
+                      const uint8_t* kind, const int32_t* cam_model, const double* intr, const double* pts,
+                      const double* uv, const double* info, double* jac) {
+    int bad = 0;
+    for (int32_t i = 0; i < n_obs; i++) {
+        double cc[sba::CAM_CACHE_STRIDE];
+        sba::pose_cache(cam_r + 3 * cam[i], cam_t + 3 * cam[i], cc);
+        if (!sba::obs_intr_jac(cc, pts + 3 * pt[i], uv[2 * i], uv[2 * i + 1], intr + 10 * cam_model[cam[i]],
+                               info ? info + 4 * i : nullptr, kind ? kind[cam[i]] : 0, jac + 20 * (size_t)i)) bad++;
+    }
+    return bad;
+}
+
 int hm_inv6(const double* A, double* Ai) { return sba::inv6_spd(A, Ai) ? 0 : 1; }
 int hm_inv3(const double* H6, double* Hi6) { return sba::inv3_sym(H6, Hi6) ? 0 : 1; }
 void hm_pose_cache(const double* r, const double* t, double* out24) { sba::pose_cache(r, t, out24); }

@@ -380,3 +380,18 @@ def test_venice_scale_explicit_tiles_against_implicit_operator(monkeypatch):
     for a, b in zip(out["1"]["cost_history"], out["0"]["cost_history"]):
         assert abs(a - b) <= 1e-11 * b
     assert all(abs(a - b) <= 1 for a, b in zip(out["1"]["pcg_iters_history"], out["0"]["pcg_iters_history"]))
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(mixed=True)])
+@pytest.mark.parametrize("with_info", [False, True])
+def test_intrinsics_jacobian(oracle, kw, with_info):
+    """SURVEY 8(f) row 1 (first half): the CUDA intrinsics-Jacobian hook against the oracle's duals over the five intrinsic blocks."""
+    sc = synthetic.make_scene("small", **kw)
+    if with_info:
+        sc["obs_info"] = np.random.default_rng(5).normal(size=(sc["n_obs"], 2, 2)) + 2 * np.eye(2)
+    jo = oracle.Problem(sc).intrinsics_jac()
+    s, _ = gpu_solver(sc)
+    j = s.intrinsics_jacobian()
+    assert j.shape == jo.shape and np.abs(j[:, :, 8:]).max() == 0.0
+    for c in range(8):
+        assert relerr(j[:, :, c], jo[:, :, c]) < TOL_J, c

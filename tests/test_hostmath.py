@@ -74,3 +74,25 @@ def test_inv6_and_inv3(hostmath):
         Hi = np.array([[hi[0], hi[1], hi[2]], [hi[1], hi[3], hi[4]], [hi[2], hi[4], hi[5]]])
         assert np.abs(Hi @ H - np.eye(3)).max() < 1e-10
     assert hostmath.hm_inv6(ptr(np.zeros((6, 6))), ptr(np.empty((6, 6)))) == 1
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(spherical=True), dict(mixed=True)])
+@pytest.mark.parametrize("with_info", [False, True])
+def test_intrinsics_jacobian_closed_form_matches_autodiff(hostmath, oracle, kw, with_info):
+    """SURVEY 8(f) row 1, first half: d res / d (f, pp, k, t, B) in closed form (obs_intr_jac) against the duals of the reference
+    functor over its five intrinsic blocks; the B columns are identically zero (pinholecameraprojectormodule.h:46-47)."""
+    sc = synthetic.make_scene("small", **kw)
+    if with_info:
+        rng = np.random.default_rng(5)
+        sc["obs_info"] = rng.normal(size=(sc["n_obs"], 2, 2)) + 2 * np.eye(2)
+    jo = oracle.Problem(sc).intrinsics_jac()
+    n = sc["obs_cam"].size
+    j = np.empty((n, 2, 10))
+    info = None if sc["obs_info"] is None else np.ascontiguousarray(sc["obs_info"], dtype=np.float64)
+    bad = hostmath.hm_intrinsics_jac(n, ptr(sc["obs_cam"]), ptr(sc["obs_pt"]), ptr(sc["raxis"]), ptr(sc["t"]), ptr(sc["cost_kind"]),
+                                     ptr(sc["cam_model"]), ptr(sc["intrinsics"]), ptr(sc["pts"]), ptr(sc["obs_uv"]), ptr(info), ptr(j))
+    assert bad == 0
+    assert np.abs(jo[:, :, 8:]).max() == 0.0 and np.abs(j[:, :, 8:]).max() == 0.0
+    # column-wise relative error: the columns span ~8 orders of magnitude (d/dpp ~ 1, d/dk3 ~ f r^6)
+    for c in range(8):
+        assert relerr(j[:, :, c], jo[:, :, c]) < TOL, c
