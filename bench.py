@@ -164,7 +164,8 @@ def bench_config(a, explicit=True):
 # --------------------------------------------------------------------------- B200 arm
 # algorithmic bytes per observation of the kernels bench.py reports on (DESIGN.md "Kernels")
 ALG_BYTES = {
-    "k_residual_jacobian": 136,      # in 16 uv + 4 idx (+ point gather from L2), out 16 res + 48 C + 48 A   (J_t = -J_X form)
+    "k_residual_jacobian": 112,      # in 16 uv + 4 idx + 4 tile slack (+ point gather from L2), out 16 res + 48 A + 24 Pbar.  SURVEY 8(d) counts 184 for the
+                                     # fully materialised Jacobian: J_t = -J_X is not stored and J_r = A [R Pbar]x Q^T is rebuilt by its readers
     "k_camera_pass": 60,             # factored form: 24 Pbar + 4 pt idx + 32 gathered y_p  (materialised form: 132)
     "k_point_pass": 56,              # 48 A planes + 4 pt idx + 4 cam idx; C x_r rebuilt as A((X-t) x R Jr x_r) (per-camera operand and the point
                                      # from L1/L2; ~26 B/obs of Hinv / y_p per point not counted)

@@ -17,7 +17,7 @@ names = {0: "K1 residual+jacobian (cam order)", 1: "K1c cost only", 5: "K1p+K2a 
          9: "K2b camera blocks", 2: "K1p+K2a+K2b", 4: "schur diag + invert",
          6: "matvec point pass", 7: "matvec camera pass", 3: "matvec S*x"}
 No = sz["n_obs"]
-bytes_per_obs = {0: 136, 1: 20 + 32, 5: 24 + 48 + 19, 9: 112, 2: 24 + 48 + 19 + 112, 6: 56, 7: 60, 3: 116}
+bytes_per_obs = {0: 112, 1: 20 + 32, 5: 24 + 48 + 19, 9: 88, 2: 24 + 48 + 19 + 88, 6: 56, 7: 60, 3: 116}
 out = {"shape": shape, "sizes": sz, "gen_s": t_gen, "ingest_s": t_fin, "stages": {}}
 for st in (0, 1, 5, 9, 2, 4, 6, 7, 3):
     ms = s.time_stage(st, reps)

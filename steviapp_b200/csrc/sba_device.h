@@ -64,10 +64,11 @@ struct DevProblem {
     double* q_info;       // 4*Nq AoS or nullptr
     // materialised linearisation
     double* res;          // 2 planes of Ns   } camera order
-    double* Cc;           // 6 planes of Ns   }   (d res / d rAxis)
     double* Ac;           // 6 planes of Ns   }   (d res / d X)
-    double* Pc;           // 3 planes of Ns: Pbar, or nullptr  } factored operator pass (identity stiffness):
-    double* Kc;           // 2 planes of Ns: Pi scale constants } A, C rebuilt from 40 B instead of read as 96 B
+    double* Pc;           // 3 planes of Ns: Pbar.  d res / d rAxis = C = A [R Pbar]x Q^T is rebuilt from A, Pbar and the camera
+                          //   (rebuild_C, sba_kernel_util.cuh) instead of being stored
+    double* Kc;           // 2 planes of Ns: Pi scale constants of spherical cameras, or nullptr (factored camera pass)
+    int32_t cp_factored;  // 1: the camera pass of the implicit operator rebuilds Pi, A, C from Pbar alone (identity stiffness)
     double* qA;           // 6 planes of Nq: point order.  C is NOT kept in point order: C x_r = A ((X - t) x (R Jr x_r)),
                           // so the point pass needs only A, the point and a 9-double per-camera operand (cam_vec)
     // ---- explicit reduced camera system (operator_mode 0 auto / 3 forced; see sba_kernels_explicit.cu) ----
@@ -178,6 +179,7 @@ void launch_prior_eval(const DevProblem& P, int store, cudaStream_t st);        
 void launch_pack_tail(const DevProblem& P, double* tail, cudaStream_t st);
 void launch_cost_reduce(const DevProblem& P, cudaStream_t st);                   // tile costs -> SC_COST_OBS
 void launch_camera_blocks(const DevProblem& P, cudaStream_t st);                 // K2b: tile partials + per-camera reduce -> Hcc, gc
+void launch_preq_finish(const DevProblem& P, double* H21, double* g6, cudaStream_t st);   // per camera: T (.) T^T, T (.) with T = diag(Q, I)
 void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st);     // add A^T A, A^T r of the priors
 void launch_scaling(const DevProblem& P, int enabled, cudaStream_t st);
 void launch_damping(const DevProblem& P, double radius, double dmin, double dmax, cudaStream_t st);

@@ -107,6 +107,84 @@ __device__ __forceinline__ void st256(double* p, double a, double b, double c, d
     asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" :: "l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
 }
 
+// C = d res / d rAxis is NOT stored in camera order: with d = X - t = R Pbar and Q = (R Jr)^T (cam_Q, written by K0)
+//   C = W Pi [Pbar]x Jr = A [d]x Q^T,   row k:  C_k = (A_k x d) Q^T
+// for ANY stiffness W, so the passes that need C rebuild it from the A planes, the Pbar planes (Pc) and two per-camera
+// 3x3 constants: 24 B/obs read instead of 48, and K1 writes 48 B/obs less.
+struct CamRQ { double Rt[9], Q[9]; };
+__device__ __forceinline__ CamRQ load_cam_rq(const DevProblem& P, int cam) {
+    CamRQ c;
+    const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+    const d4 a0 = ld256(cc), a1 = ld256(cc + 4), a2 = ld256(cc + 8);
+    c.Rt[0] = a0.x; c.Rt[1] = a0.y; c.Rt[2] = a0.z; c.Rt[3] = a0.w; c.Rt[4] = a1.x; c.Rt[5] = a1.y; c.Rt[6] = a1.z; c.Rt[7] = a1.w; c.Rt[8] = a2.x;
+    const double* q = P.cam_Q + 12 * (size_t)cam;
+    const d4 q0 = ld256(q), q1 = ld256(q + 4), q2 = ld256(q + 8);
+    c.Q[0] = q0.x; c.Q[1] = q0.y; c.Q[2] = q0.z; c.Q[3] = q0.w; c.Q[4] = q1.x; c.Q[5] = q1.y; c.Q[6] = q1.z; c.Q[7] = q1.w; c.Q[8] = q2.x;
+    return c;
+}
+// A: rows (A[0..2]), (A[3..5]); Pb = Pbar of the slot; C out in the same layout
+__device__ __forceinline__ void rebuild_C(const double* A, double p0, double p1, double p2, const CamRQ& c, double* C) {
+    const double d0 = c.Rt[0] * p0 + c.Rt[3] * p1 + c.Rt[6] * p2;   // d = R Pbar, R = Rt^T
+    const double d1 = c.Rt[1] * p0 + c.Rt[4] * p1 + c.Rt[7] * p2;
+    const double d2 = c.Rt[2] * p0 + c.Rt[5] * p1 + c.Rt[8] * p2;
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const double a0 = A[3 * r], a1 = A[3 * r + 1], a2 = A[3 * r + 2];
+        const double w0 = a1 * d2 - a2 * d1, w1 = a2 * d0 - a0 * d2, w2 = a0 * d1 - a1 * d0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) C[3 * r + k] = w0 * c.Q[3 * k] + w1 * c.Q[3 * k + 1] + w2 * c.Q[3 * k + 2];
+    }
+}
+
+// Cheaper form for the passes that SUM over the observations of one camera: C_k = w_k Q^T with w_k = A_k x d, and Q is a
+// per-camera constant, so they accumulate with the "pre-Q" rows J' = [w | -A] (21 FMA per observation instead of 39) and
+// apply T = diag(Q, I) once per camera:  sum Jc^T M Jc = T (sum J'^T M J') T^T,  sum Jc^T r = T sum J'^T r.
+__device__ __forceinline__ void preq_rows(const double* A, double p0, double p1, double p2, const double* Rt, double* w) {
+    const double d0 = Rt[0] * p0 + Rt[3] * p1 + Rt[6] * p2;   // d = R Pbar, R = Rt^T
+    const double d1 = Rt[1] * p0 + Rt[4] * p1 + Rt[7] * p2;
+    const double d2 = Rt[2] * p0 + Rt[5] * p1 + Rt[8] * p2;
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const double a0 = A[3 * r], a1 = A[3 * r + 1], a2 = A[3 * r + 2];
+        w[3 * r] = a1 * d2 - a2 * d1; w[3 * r + 1] = a2 * d0 - a0 * d2; w[3 * r + 2] = a0 * d1 - a1 * d0;
+    }
+}
+__device__ __forceinline__ void load_rt(const DevProblem& P, int cam, double* Rt) {
+    const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+    const d4 a0 = ld256(cc), a1 = ld256(cc + 4), a2 = ld256(cc + 8);
+    Rt[0] = a0.x; Rt[1] = a0.y; Rt[2] = a0.z; Rt[3] = a0.w; Rt[4] = a1.x; Rt[5] = a1.y; Rt[6] = a1.z; Rt[7] = a1.w; Rt[8] = a2.x;
+}
+// in place: packed symmetric 6x6 H' (21, row-major upper) -> T H' T^T, and g' (6) -> T g' (either may be null), T = diag(Q, I)
+__device__ __forceinline__ void preq_finish(const double* Q, double* H21, double* g6) {
+    if (H21) {
+        double M[36];
+        int q = 0;
+#pragma unroll
+        for (int a = 0; a < 6; a++)
+#pragma unroll
+            for (int b = a; b < 6; b++) { M[6 * a + b] = H21[q]; M[6 * b + a] = H21[q]; q++; }
+        double L[36];   // L = T M: rows 0..2 mixed by Q
+#pragma unroll
+        for (int c = 0; c < 6; c++) {
+#pragma unroll
+            for (int r = 0; r < 3; r++) L[6 * r + c] = Q[3 * r] * M[c] + Q[3 * r + 1] * M[6 + c] + Q[3 * r + 2] * M[12 + c];
+#pragma unroll
+            for (int r = 3; r < 6; r++) L[6 * r + c] = M[6 * r + c];
+        }
+        q = 0;   // (L T^T)[a][b] for b >= a: columns 0..2 mixed by Q
+#pragma unroll
+        for (int a = 0; a < 6; a++)
+#pragma unroll
+            for (int b = a; b < 6; b++) {
+                H21[q++] = b < 3 ? L[6 * a] * Q[3 * b] + L[6 * a + 1] * Q[3 * b + 1] + L[6 * a + 2] * Q[3 * b + 2] : L[6 * a + b];
+            }
+    }
+    if (g6) {
+        const double g0 = g6[0], g1 = g6[1], g2 = g6[2];
+        g6[0] = Q[0] * g0 + Q[1] * g1 + Q[2] * g2; g6[1] = Q[3] * g0 + Q[4] * g1 + Q[5] * g2; g6[2] = Q[6] * g0 + Q[7] * g1 + Q[8] * g2;
+    }
+}
+
 // per-camera operand of the point pass (sba_kernels_points.cu) for the input vector x6 = (x_r, x_t) of camera c:
 //   (a_c = R Jr x_r, g_c = x_t + (t - c0) x a_c, pad 2)   -- 64 B, two 256-bit loads --
 // so that  C x_r - A x_t = A ((X - t) x a_c - x_t) = A ((X - c0) x a_c - g_c).  c0 = P.center (fixed at finalize, the

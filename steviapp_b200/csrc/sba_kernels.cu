@@ -43,9 +43,10 @@ void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
 // memory once per tile, (u,v) fetched with one 128-bit load per observation,
 // the point with two 128-bit loads (one 32 B sector), outputs written as
 // coalesced SoA planes.  JAC=false is the cost-only variant K1c (trial steps).
-// Algorithmic bytes per observation: in 16 (uv) + 4 (pt); out 16 (res) + 48 (C)
-// + 48 (A) = 132 (+4 B/obs index) -- the "136 B/obs" form of SURVEY 8(d)
-// (J_t = -J_X not stored; 184 B/obs with it).
+// Algorithmic bytes per observation: in 16 (uv) + 4 (pt); out 16 (res) + 48 (A)
+// + 24 (Pbar) = 108 (+4 B/obs index) = 112 B/obs.  SURVEY 8(d) counts 184 B/obs for the fully
+// materialised Jacobian; here J_t = -J_X is not stored and J_r = A [R Pbar]x Q^T is rebuilt by its
+// readers from A and Pbar (rebuild_C), so 72 B/obs of it never exist.
 // ---------------------------------------------------------------------------
 template <bool JAC>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(DevProblem P) {
@@ -80,7 +81,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
             Wp = W;
         }
         double r[2] = {0.0, 0.0}, Jc[12], Jp[6], aux[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp, (JAC && P.Pc) ? aux : nullptr);
+        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp, JAC ? aux : nullptr);
         if (!ok) {
             bad = 1;
             aux[0] = aux[1] = aux[2] = 0.0;   // Pbar = 0 marks a failed row for the factored pass
@@ -98,15 +99,11 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(D
             stcs(P.res + (Ns + s), r[1]);
 #pragma unroll
             for (int j = 0; j < 3; j++) {
-                stcs(P.Cc + ((size_t)j * Ns + s), Jc[j]);
-                stcs(P.Cc + ((size_t)(3 + j) * Ns + s), Jc[6 + j]);
                 stcs(P.Ac + ((size_t)j * Ns + s), Jp[j]);
                 stcs(P.Ac + ((size_t)(3 + j) * Ns + s), Jp[3 + j]);
             }
-            if (P.Pc) {
-                stcs(P.Pc + (s), aux[0]); stcs(P.Pc + (Ns + s), aux[1]); stcs(P.Pc + (2 * Ns + s), aux[2]);
-                if (P.Kc) { stcs(P.Kc + (s), aux[3]); stcs(P.Kc + (Ns + s), aux[4]); }
-            }
+            stcs(P.Pc + (s), aux[0]); stcs(P.Pc + (Ns + s), aux[1]); stcs(P.Pc + (2 * Ns + s), aux[2]);
+            if (P.Kc) { stcs(P.Kc + (s), aux[3]); stcs(P.Kc + (Ns + s), aux[4]); }
         }
     }
     acc = warp_sum(acc);

@@ -59,18 +59,30 @@ __global__ void k_gather_outputs(DevProblem P, const int32_t* __restrict__ slot_
                                  double* jc_out, double* jp_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= P.No) return;
-    const size_t s = slot_of_obs[i], Ns = (size_t)P.Ns;
+    const int si = slot_of_obs[i];
+    const size_t s = si, Ns = (size_t)P.Ns;
     if (res_out) { res_out[2 * (size_t)i] = P.res[s]; res_out[2 * (size_t)i + 1] = P.res[Ns + s]; }
+    double A[6], C[6];
+#pragma unroll
+    for (int a = 0; a < 6; a++) A[a] = P.Ac[(size_t)a * Ns + s];
+    if (jc_out) {
+        int lo = 0, hi = P.Nt - 1;
+        while (lo < hi) {   // camera of the slot: last tile with tile_start <= s
+            const int mid = (lo + hi + 1) >> 1;
+            if (__ldg(P.tile_start + mid) <= si) lo = mid; else hi = mid - 1;
+        }
+        const CamRQ crq = load_cam_rq(P, __ldg(P.tile_cam + lo));
+        rebuild_C(A, P.Pc[s], P.Pc[Ns + s], P.Pc[2 * Ns + s], crq, C);
+    }
 #pragma unroll
     for (int row = 0; row < 2; row++)
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            const double A = P.Ac[(size_t)(3 * row + a) * Ns + s];
             if (jc_out) {
-                jc_out[12 * (size_t)i + 6 * row + a] = P.Cc[(size_t)(3 * row + a) * Ns + s];
-                jc_out[12 * (size_t)i + 6 * row + 3 + a] = -A;
+                jc_out[12 * (size_t)i + 6 * row + a] = C[3 * row + a];
+                jc_out[12 * (size_t)i + 6 * row + 3 + a] = -A[3 * row + a];
             }
-            if (jp_out) jp_out[6 * (size_t)i + 3 * row + a] = A;
+            if (jp_out) jp_out[6 * (size_t)i + 3 * row + a] = A[3 * row + a];
         }
 }
 void launch_gather_outputs(const DevProblem& P, const int32_t* slot_of_obs, double* res_out, double* jc_out,

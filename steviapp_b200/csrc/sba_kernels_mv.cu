@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
     if (tile >= P.Nt) return;
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
+    const CamRQ crq = load_cam_rq(P, __ldg(P.tile_cam + tile));
     double w[6] = {0, 0, 0, 0, 0, 0};
     for (int s = start + lane; s < start + len; s += 32) {
         const int pt = __ldcs(P.obs_pt + s);
@@ -22,10 +23,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_pass(DevProblem
         const d4 y = ld256(P.y_p + 4 * (size_t)pt);
         double A[6], C[6];
 #pragma unroll
-        for (int a = 0; a < 6; a++) {
-            A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
-            C[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
-        }
+        for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+        rebuild_C(A, __ldcs(P.Pc + s), __ldcs(P.Pc + Ns + s), __ldcs(P.Pc + 2 * Ns + s), crq, C);
         const double b0 = A[0] * y.x + A[1] * y.y + A[2] * y.z;
         const double b1 = A[3] * y.x + A[4] * y.y + A[5] * y.z;
 #pragma unroll
@@ -154,7 +153,7 @@ __global__ void k_camera_finish(DevProblem P, const double* x, const double* bas
 }
 void launch_camera_pass_tiles(const DevProblem& P, cudaStream_t st) {
     if (!P.Nt) return;
-    if (P.Pc) {
+    if (P.cp_factored) {
         const int nb = cdiv(P.Nt, WARPS_PER_BLOCK);
         if (P.cp_variant == 1) k_camera_pass_f<4><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
         else if (P.cp_variant == 2) k_camera_pass_f<1><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);

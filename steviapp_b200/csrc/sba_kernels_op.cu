@@ -89,6 +89,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_schur_diag(DevProblem 
     if (tile >= P.Nt) return;
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
+    double Rt[9];
+    load_rt(P, __ldg(P.tile_cam + tile), Rt);
     double D[21];
 #pragma unroll
     for (int i = 0; i < 21; i++) D[i] = 0.0;
@@ -97,16 +99,12 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_schur_diag(DevProblem 
         if (pt < 0) continue;
         const double* Hp = P.Hinv + 8 * (size_t)pt;
         const double2 h01 = ldg2(Hp), h23 = ldg2(Hp + 2), h45 = ldg2(Hp + 4);
-        double A[6], j0[6], j1[6];
+        double A[6], w[6], j0[6], j1[6];   // pre-Q rows J' = [A x d | -A]; diag(Q, I) is applied per camera after the tile sum
 #pragma unroll
-        for (int a = 0; a < 3; a++) {
-            A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
-            A[3 + a] = __ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
-            j0[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
-            j1[a] = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
-            j0[3 + a] = -A[a];
-            j1[3 + a] = -A[3 + a];
-        }
+        for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+        preq_rows(A, __ldcs(P.Pc + s), __ldcs(P.Pc + Ns + s), __ldcs(P.Pc + 2 * Ns + s), Rt, w);
+#pragma unroll
+        for (int a = 0; a < 3; a++) { j0[a] = w[a]; j1[a] = w[3 + a]; j0[3 + a] = -A[a]; j1[3 + a] = -A[3 + a]; }
         // BH = A * Hinv (2x3), T = BH * A^T (2x2)
         const double b00 = A[0] * h01.x + A[1] * h01.y + A[2] * h23.x;
         const double b01 = A[0] * h01.y + A[1] * h23.y + A[2] * h45.x;
@@ -144,6 +142,7 @@ __global__ void k_tile_reduce21(DevProblem P, double* dst) {
 void launch_schur_diag(const DevProblem& P, cudaStream_t st) {
     if (P.Nt) k_schur_diag<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
     k_tile_reduce21<<<cdiv(P.Nc * 21, 256), 256, 0, st>>>(P, P.Sd);
+    launch_preq_finish(P, P.Sd, nullptr, st);
 }
 
 // Minv = (Hcc + lam_c - Sd)^-1 per camera (6x6 Cholesky in registers)

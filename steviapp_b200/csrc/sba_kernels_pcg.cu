@@ -311,20 +311,26 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
     double x[6];
 #pragma unroll
     for (int a = 0; a < 6; a++) x[a] = dc[6 * (size_t)cam + a];
+    // C x_r = (A [d]x Q^T) x_r = A (d x a_c), a_c = Q^T x_r (per camera), d = R Pbar: no C planes needed
+    const CamRQ crq = load_cam_rq(P, cam);
+    const double ac0 = crq.Q[0] * x[0] + crq.Q[3] * x[1] + crq.Q[6] * x[2];
+    const double ac1 = crq.Q[1] * x[0] + crq.Q[4] * x[1] + crq.Q[7] * x[2];
+    const double ac2 = crq.Q[2] * x[0] + crq.Q[5] * x[1] + crq.Q[8] * x[2];
     double acc = 0.0;
     for (int s = start + lane; s < start + len; s += 32) {
         const int pt = __ldcs(P.obs_pt + s);
         if (pt < 0) continue;
         const double2 d01 = ldg2(P.dp + 4 * (size_t)pt), d23 = ldg2(P.dp + 4 * (size_t)pt + 2);
-        double m0 = 0.0, m1 = 0.0;
+        double m0 = 0.0, m1 = 0.0, A[6];
 #pragma unroll
-        for (int a = 0; a < 3; a++) {
-            const double A0 = __ldcs(P.Ac + (size_t)a * Ns + s), A1 = __ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
-            const double C0 = __ldcs(P.Cc + (size_t)a * Ns + s), C1 = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
-            const double dpa = a == 0 ? d01.x : (a == 1 ? d01.y : d23.x);
-            m0 += C0 * x[a] + A0 * (dpa - x[3 + a]);
-            m1 += C1 * x[a] + A1 * (dpa - x[3 + a]);
-        }
+        for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+        const double p0 = __ldcs(P.Pc + s), p1 = __ldcs(P.Pc + Ns + s), p2 = __ldcs(P.Pc + 2 * Ns + s);
+        const double d0 = crq.Rt[0] * p0 + crq.Rt[3] * p1 + crq.Rt[6] * p2;
+        const double d1 = crq.Rt[1] * p0 + crq.Rt[4] * p1 + crq.Rt[7] * p2;
+        const double d2 = crq.Rt[2] * p0 + crq.Rt[5] * p1 + crq.Rt[8] * p2;
+        const double v[3] = {d1 * ac2 - d2 * ac1 + d01.x - x[3], d2 * ac0 - d0 * ac2 + d01.y - x[4], d0 * ac1 - d1 * ac0 + d23.x - x[5]};
+#pragma unroll
+        for (int a = 0; a < 3; a++) { m0 += A[a] * v[a]; m1 += A[3 + a] * v[a]; }
         const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
         acc += m0 * (r0 + 0.5 * m0) + m1 * (r1 + 0.5 * m1);
     }

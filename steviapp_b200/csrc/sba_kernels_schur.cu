@@ -102,7 +102,7 @@ void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st) {
 // Jc^T Jc (21 unique) and Jc^T res (6) with Jc = [C | -A]; a fixed xor-shuffle
 // tree folds the 32 lanes; lane 0 writes the tile partial.  k_tile_reduce then
 // sums the tiles of each camera in tile order.
-// Reads 112 B/obs (res, C, A planes, coalesced).
+// Reads 88 B/obs (res, A, Pbar planes, coalesced); C rebuilt in registers.
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProblem P) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -110,19 +110,22 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProbl
     if (tile >= P.Nt) return;
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
+    double Rt[9];
+    load_rt(P, __ldg(P.tile_cam + tile), Rt);
     double H[21], g[6];
 #pragma unroll
     for (int i = 0; i < 21; i++) H[i] = 0.0;
 #pragma unroll
     for (int i = 0; i < 6; i++) g[i] = 0.0;
     for (int s = start + lane; s < start + len; s += 32) {
-        double j0[6], j1[6];   // the two rows of Jc
+        double j0[6], j1[6];   // the two pre-Q rows J' = [A x d | -A] (Jc = J' diag(Q, I)^T, applied per camera by k_preq_finish)
+        {
+            double A[6], w[6];
 #pragma unroll
-        for (int a = 0; a < 3; a++) {
-            j0[a] = __ldcs(P.Cc + (size_t)a * Ns + s);
-            j1[a] = __ldcs(P.Cc + (size_t)(3 + a) * Ns + s);
-            j0[3 + a] = -__ldcs(P.Ac + (size_t)a * Ns + s);
-            j1[3 + a] = -__ldcs(P.Ac + (size_t)(3 + a) * Ns + s);
+            for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+            preq_rows(A, __ldcs(P.Pc + s), __ldcs(P.Pc + Ns + s), __ldcs(P.Pc + 2 * Ns + s), Rt, w);
+#pragma unroll
+            for (int a = 0; a < 3; a++) { j0[a] = w[a]; j1[a] = w[3 + a]; j0[3 + a] = -A[a]; j1[3 + a] = -A[3 + a]; }
         }
         const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
         int q = 0;
@@ -153,10 +156,36 @@ __global__ void k_tile_reduce(DevProblem P, int src, int n, double* dst, int zer
     }
     dst[i] = acc;
 }
+// thread per camera: pre-Q sums -> T (.) T^T / T (.), T = diag(Q, I) of the camera (see preq_finish)
+__global__ void k_preq_finish(DevProblem P, double* H21, double* g6) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.Nc) return;
+    double Q[9], H[21], g[6];
+    const double* q = P.cam_Q + 12 * (size_t)c;
+#pragma unroll
+    for (int i = 0; i < 9; i++) Q[i] = q[i];
+#pragma unroll
+    for (int i = 0; i < 21; i++) H[i] = H21[21 * (size_t)c + i];
+    if (g6) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) g[i] = g6[6 * (size_t)c + i];
+    }
+    preq_finish(Q, H, g6 ? g : nullptr);
+#pragma unroll
+    for (int i = 0; i < 21; i++) H21[21 * (size_t)c + i] = H[i];
+    if (g6) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) g6[6 * (size_t)c + i] = g[i];
+    }
+}
+void launch_preq_finish(const DevProblem& P, double* H21, double* g6, cudaStream_t st) {
+    k_preq_finish<<<cdiv(P.Nc, 128), 128, 0, st>>>(P, H21, g6);
+}
 void launch_camera_blocks(const DevProblem& P, cudaStream_t st) {
     if (P.Nt) k_camera_blocks<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
     k_tile_reduce<<<cdiv(P.Nc * 21, 256), 256, 0, st>>>(P, 0, 21, P.Hcc, 1);
     k_tile_reduce<<<cdiv(P.Nc * 6, 256), 256, 0, st>>>(P, 21, 6, P.gc, 1);
+    launch_preq_finish(P, P.Hcc, P.gc, st);
 }
 
 }  // namespace sba
