@@ -49,7 +49,7 @@ void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
 // readers from A and Pbar (rebuild_C), so 72 B/obs of it never exist.
 // ---------------------------------------------------------------------------
 template <bool JAC>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 3) k_residual_jacobian(DevProblem P) {
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 4) k_residual_jacobian(DevProblem P) {
     __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
