@@ -25,6 +25,7 @@ import numpy as np  # noqa: E402
 METRIC = "lm_iterations_per_s"
 UNIT = "LM iters/s"
 FIXED = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
+LM_CHUNK = 6             # LM iterations per uninterrupted solve of the timed region (restart from the initial values in between)
 SAMPLE_DIV = 16          # CPU legs run on a Venice-shape scene with 1/16 of the points (same cameras, same views/point)
 
 
@@ -155,7 +156,7 @@ def bench_config(a, explicit=True):
                              ("Schur complement + SCHUR_JACOBI PCG; implicit operator (two passes over the observations per CG iteration: the explicit "
                               "tiles would be a larger stream than the observations); multi-GPU: the 6*Nc partial is all-reduced inside the fused PCG "
                               "kernel over NVLink peer mailboxes"),
-            "step": "one LM iteration, fixed count (tolerances 0), every run restarts from the same initial values",
+            "step": "one LM iteration, fixed count (tolerances 0); solves of at most 6 LM iterations, each restarting from the same initial values",
             "l2": ("inputs larger than L2, no flush: ~1.2 GB of observation planes per linearisation and 479 MB of tiles per CG iteration vs 126 MB L2; "
                    "inside a PCG solve 80 MB of the tiles are deliberately kept L2-resident (evict_last) across its CG iterations"),
             "parallelism": f"points sharded over {a.gpus} GPU(s), cameras replicated"}
@@ -230,16 +231,32 @@ def run_b200(a):
     if a.warmup > 0:
         s.solve(max_iterations=a.warmup, copy_params=False)
 
-    # ---- `value`: K LM iterations, inputs resident in HBM, device time (CUDA events on the solver's stream)
-    reset()
-    barrier()
-    with ClockSampler(local) as clk:
-        w0 = time.perf_counter()
-        r = s.solve(max_iterations=a.steps, copy_params=False)
-        barrier()
-        wall = time.perf_counter() - w0
-    assert r["iterations"] == a.steps, r
-    ms_total = maxr(r["ms_total"])
+    # ---- `value`: K LM iterations, inputs resident in HBM, device time (CUDA events on the solver's stream).  The LM runs in
+    # chunks of at most LM_CHUNK iterations, every chunk restarting from the same initial values (a longer uninterrupted run
+    # converges to machine precision and stops taking steps); the parameter re-upload between chunks is outside the device time.
+    r = None
+    ms_total = 0.0
+    wall = 0.0
+    done = 0
+    clk = ClockSampler(local)
+    with clk:
+        while done < a.steps:
+            n = min(LM_CHUNK, a.steps - done)
+            reset()
+            barrier()
+            w0 = time.perf_counter()
+            rc = s.solve(max_iterations=n, copy_params=False)
+            barrier()
+            wall += time.perf_counter() - w0
+            assert rc["iterations"] == n, rc
+            ms_total += maxr(rc["ms_total"])
+            done += n
+            if r is None:
+                r = rc
+            else:   # accumulate what the report uses
+                for k in ("iterations", "pcg_iterations_total", "kernel_launches", "ms_total", "ms_linearize", "ms_schur", "ms_pcg", "ms_update"):
+                    r[k] += rc[k]
+                r["final_cost"] = rc["final_cost"]
     wall = maxr(wall)
     value = a.steps / (ms_total * 1e-3)
     final_cost = r["final_cost"]
