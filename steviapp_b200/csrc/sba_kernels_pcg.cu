@@ -308,14 +308,13 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
     const int cam = __ldg(P.tile_cam + tile);
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
-    double x[6];
-#pragma unroll
-    for (int a = 0; a < 6; a++) x[a] = dc[6 * (size_t)cam + a];
-    // C x_r = (A [d]x Q^T) x_r = A (d x a_c), a_c = Q^T x_r (per camera), d = R Pbar: no C planes needed
-    const CamRQ crq = load_cam_rq(P, cam);
-    const double ac0 = crq.Q[0] * x[0] + crq.Q[3] * x[1] + crq.Q[6] * x[2];
-    const double ac1 = crq.Q[1] * x[0] + crq.Q[4] * x[1] + crq.Q[7] * x[2];
-    const double ac2 = crq.Q[2] * x[0] + crq.Q[5] * x[1] + crq.Q[8] * x[2];
+    // m = Jc dc + Jp dp = A ((X - t) x a_c - x_t + dp) = A ((X - c0) x a_c - g_c + dp) with the per-camera operand (a_c, g_c) of dc
+    // (cam_vec, written by launch_model_change), X - c0 = R Pbar + (t - c0): no C planes, no per-tile 3x3 products
+    const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+    const d4 r0 = ld256(cc), r1 = ld256(cc + 4), r2 = ld256(cc + 8);   // Rt (9), t (3)
+    const d4 o0 = ld256(P.cam_vec + (size_t)CAM_VEC_STRIDE * cam), o1 = ld256(P.cam_vec + (size_t)CAM_VEC_STRIDE * cam + 4);
+    const double ac0 = o0.x, ac1 = o0.y, ac2 = o0.z, gc0 = o0.w, gc1 = o1.x, gc2 = o1.y;
+    const double tc0 = r2.y - P.center[0], tc1 = r2.z - P.center[1], tc2 = r2.w - P.center[2];
     double acc = 0.0;
     for (int s = start + lane; s < start + len; s += 32) {
         const int pt = __ldcs(P.obs_pt + s);
@@ -325,14 +324,14 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
 #pragma unroll
         for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
         const double p0 = __ldcs(P.Pc + s), p1 = __ldcs(P.Pc + Ns + s), p2 = __ldcs(P.Pc + 2 * Ns + s);
-        const double d0 = crq.Rt[0] * p0 + crq.Rt[3] * p1 + crq.Rt[6] * p2;
-        const double d1 = crq.Rt[1] * p0 + crq.Rt[4] * p1 + crq.Rt[7] * p2;
-        const double d2 = crq.Rt[2] * p0 + crq.Rt[5] * p1 + crq.Rt[8] * p2;
-        const double v[3] = {d1 * ac2 - d2 * ac1 + d01.x - x[3], d2 * ac0 - d0 * ac2 + d01.y - x[4], d0 * ac1 - d1 * ac0 + d23.x - x[5]};
+        const double d0 = r0.x * p0 + r0.w * p1 + r1.z * p2 + tc0;   // X - c0 = R Pbar + (t - c0), R = Rt^T
+        const double d1 = r0.y * p0 + r1.x * p1 + r1.w * p2 + tc1;
+        const double d2 = r0.z * p0 + r1.y * p1 + r2.x * p2 + tc2;
+        const double v[3] = {d1 * ac2 - d2 * ac1 - gc0 + d01.x, d2 * ac0 - d0 * ac2 - gc1 + d01.y, d0 * ac1 - d1 * ac0 - gc2 + d23.x};
 #pragma unroll
         for (int a = 0; a < 3; a++) { m0 += A[a] * v[a]; m1 += A[3 + a] * v[a]; }
-        const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
-        acc += m0 * (r0 + 0.5 * m0) + m1 * (r1 + 0.5 * m1);
+        const double e0 = __ldcs(P.res + s), e1 = __ldcs(P.res + Ns + s);
+        acc += m0 * (e0 + 0.5 * m0) + m1 * (e1 + 0.5 * m1);
     }
     acc = warp_sum(acc);
     if (lane == 0) P.tile_cost[tile] = acc;
@@ -405,6 +404,7 @@ __global__ void __launch_bounds__(RED_BLOCK) k_model_reduce(DevProblem P, const 
     }
 }
 void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st) {
+    launch_cam_vec(P, dc, st);   // per-camera operand (a_c, g_c) of dc for k_model_tiles
     if (P.Nt) k_model_tiles<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P, dc);
     if (P.NB) k_point_stats<<<P.NB, 256, 0, st>>>(P);
     k_model_reduce<<<1, RED_BLOCK, 0, st>>>(P, dc);
