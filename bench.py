@@ -321,6 +321,19 @@ def run_b200(a):
                                    "note": ("slice of the tiles < 126 MB L2: re-read from L2 after the first CG iteration, the HBM roofline does not bound it"
                                             if shard["n_own"] * TILE_BYTES < 120e6 else "tiles streamed from HBM every CG iteration; the leading 80 MB are loaded evict_last and re-read from L2, so the "
                                                  "algorithmic rate can exceed the HBM peak (roofline.traffic = DRAM bytes measured by ncu)")}
+            sp = s.explicit_sparse_info()
+            if sp["enabled"]:
+                # block-sparse panels: the kernel streams only the 6x6 blocks of camera pairs that share a point.  Algorithmic
+                # bytes = the values of those blocks (288 B each), once per CG iteration; the stream adds the 16-bit column
+                # maps, headers and 128-byte padding (stream_bytes).  dense_equivalent = the rate the dense tiles would need.
+                per_it = 288 * sp["n_blocks"]
+                kern["k_pcg_solve"].update({
+                    "GBps": pcg_per_step * per_it / (ms * 1e-3) / 1e9, "alg_bytes_per_launch": pcg_per_step * per_it,
+                    "alg_bytes_per_cg_iteration": per_it, "stream_bytes_per_cg_iteration": sp["stream_bytes"],
+                    "blocks": sp["n_blocks"], "panels": sp["n_panels"], "chunks": sp["n_chunks"], "tile_format": "block-sparse panels",
+                    "dense_equivalent_GBps": nbytes / (ms * 1e-3) / 1e9,
+                    "note": "block-sparse panels streamed from HBM every CG iteration through a byte ring of bulk copies; the leading 80 MB are loaded "
+                            "evict_last and re-read from L2; dense_equivalent_GBps = dense tile bytes / time, for comparison with the dense-tile runs"})
             kern["k_explicit_matvec"]["note"] = "stand-alone tile mat-vec kernel (operator hook / fallback), not launched by the PCG"
             share = {"k_pcg_solve": ms, "explicit_build": kern["explicit_build"]["ms"], "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
     else:
@@ -328,7 +341,8 @@ def run_b200(a):
     dom = max(share, key=share.get)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(
+            dom + "_sparse" if kern[dom].get("tile_format") == "block-sparse panels" else dom)
         if isinstance(traffic, dict):   # persistent kernel: ncu measured one launch of 114 CG iterations; per launch of THIS run
             traffic = traffic["bytes_per_cg_iteration"] * pcg_per_step * (shard["n_own"] / max(ex["n_tiles"], 1))
     except Exception:

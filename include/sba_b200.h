@@ -250,6 +250,15 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles,
 int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange,
                        int32_t* persistent_pcg);
 
+/* block-sparse copy of the tiles (one GPU, persistent PCG kernel): the CG iterations stream, per tile and block row, only the
+ * 6x6 blocks that can be non-zero (two cameras that share a point) as PANELS of 6 rows with a 16-bit column map; consecutive
+ * panels of a tile travel in CHUNKS of <= 19 KB (one bulk copy each).  enabled = 1 when that copy is what k_pcg_solve reads
+ * (default: tiles >= 64 MB and panels <= 85 % of them; SBA_PS_SPARSE=0/1 forces); n_blocks = blocks kept; stream_bytes =
+ * bytes one CG iteration reads.  Same role as the block structure of Ceres' BlockRandomAccessSparseMatrix behind
+ * modularsbasolver.cpp:938.  Measurement only. */
+int sba_explicit_sparse_info(const sba_solver* s, int32_t* enabled, int32_t* n_panels, int32_t* n_chunks,
+                             int64_t* n_blocks, int64_t* stream_bytes);
+
 /* inspection hook: copies the tiles of the explicit reduced camera system as last built (n_tiles * 384 * 384 doubles,
  * row-major tiles; tile t covers camera tiles (tile_i[t], tile_j[t]), i <= j; diagonal tiles hold S_ii / 2 on their
  * block diagonal and zeros below) and the reduced right-hand side (6 * n_cams).  Any pointer may be NULL.  The analogue

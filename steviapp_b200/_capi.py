@@ -24,7 +24,7 @@ EXPORTS = [
     "sba_finalize", "sba_upload_parameters", "sba_download_parameters", "sba_evaluate",
     "sba_evaluate_intrinsics_jacobian", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
-    "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_tiles", "sba_version",
+    "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
 ]
 
 
@@ -108,6 +108,7 @@ def load():
     lib.sba_explicit_info.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
     lib.sba_evaluate_intrinsics_jacobian.argtypes = [vp, vp]
     lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
+    lib.sba_explicit_sparse_info.argtypes = [vp, P(i32), P(i32), P(i32), P(C.c_int64), P(C.c_int64)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

@@ -133,6 +133,15 @@ int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own,
     return SBA_OK;
 }
 
+int sba_explicit_sparse_info(const sba_solver* s, int32_t* enabled, int32_t* n_panels, int32_t* n_chunks, int64_t* n_blocks, int64_t* stream_bytes) {
+    GUARD(s);
+    const sba::DevProblem& P = s->impl.P;
+    const bool on = P.ex_on && P.ps_on && P.sp_on;
+    if (enabled) *enabled = on ? 1 : 0; if (n_panels) *n_panels = on ? P.sp_npanel : 0; if (n_chunks) *n_chunks = on ? P.sp_nchunk : 0;
+    if (n_blocks) *n_blocks = on ? P.sp_nblocks : 0; if (stream_bytes) *stream_bytes = on ? P.sp_bytes : 0;
+    return SBA_OK;
+}
+
 int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* tile_j, double* rhs) {
     GUARD(s);
     const sba::DevProblem& P = s->impl.P;

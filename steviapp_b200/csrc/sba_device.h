@@ -128,6 +128,25 @@ struct DevProblem {
     double* ps_rz;        // ps_nitems: per-item part of r.z
     double* ps_clock;     // 4: ns CTA 0 spent in (mat-vec, barrier 1, fold + vector part, barrier 2) during the last solve
     double* pcg_p2;       // 6*Nc: second copy of p (directions alternate between pcg_p and pcg_p2)
+    // ---- block-sparse copy of the tiles for the persistent PCG kernel (single GPU; sba_kernels_pcgsolve.cu, SPARSE) ----
+    // 31 % of the 6x6 blocks of the Venice-shape S are structurally zero.  After every build the dense tiles are compacted into
+    // PANELS: per (tile, block row) the non-zero block columns only, 6 rows x m6 doubles row-major, plus a 16-bit map
+    // panel column -> tile column; the CG iterations stream the panels instead of the dense rows.
+    int32_t sp_on;
+    int32_t sp_npanel;    // non-empty block rows
+    int32_t sp_nseg;      // segments = runs of panels of one CTA inside one tile
+    int32_t sp_nchunk;
+    int64_t sp_bytes;     // bytes of the panel stream (what one CG iteration reads)
+    int64_t sp_nblocks;   // 6x6 blocks kept (structurally non-zero, upper triangle + diagonal)
+    int4* sp_chunk;       // per chunk = consecutive panels of a tile that travel as one bulk copy: x stream offset / 16, y bytes, z panels, w first panel
+    int4* sp_panel;       // per panel: x stream offset and y map offset in 16-byte units, z m6 = 6 * non-zero blocks, w tile * 64 + block row
+    double* sp_data;      // the stream the CG iterations read, panel after panel: 16-byte header {first row in the tile, m6}, 6 rows x m6 doubles, column map
+    uint16_t* sp_idx;     // static part, panel after panel: the header, then the tile column of every panel column (padded to 16 B)
+    int32_t* sp_seg_ptr;  // ps_grid + 1
+    int32_t* sp_seg;      // 4 per segment: local tile, first chunk, end chunk, pad
+    double* sp_part;      // ex_nown * 384 row partials, then sp_nseg * 384 column partials
+    int32_t* sp_fold_ptr; // ex_NT + 1
+    int32_t* sp_fold_off;
     // priors, grouped by target: group g covers priors pg_off[g]..pg_off[g+1]
     int32_t Ngroup;
     int32_t* pg_off;      // Ngroup+1
@@ -235,6 +254,7 @@ void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
 // explicit reduced camera system
 void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> off-diagonal blocks of ex_S (needs Hinv of this LM iteration)
+void launch_explicit_compact(const DevProblem& P, cudaStream_t st);   // dense tiles -> block-sparse panels (sp_on)
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st);      // diagonal blocks of the owned tiles (needs Hcc, Sd, lam_c; multi-GPU: after the reduce-scatter)
 void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg = 0, double tol2 = 0.0,
                             int max_iters = 0);   // tile partials ex_row / ex_col of S x (pcg: skip once the PCG is frozen)

@@ -183,6 +183,34 @@ void launch_explicit_diag(const DevProblem& P, cudaStream_t st) {
     k_explicit_diag<<<cdiv(P.Nc * 36, 256), 256, 0, st>>>(P);
 }
 
+// dense tiles -> block-sparse panels of the persistent PCG kernel (sp_on): one warp per panel copies the 6 rows of the
+// block row through the panel's column map (48-byte runs of a tile row -> contiguous panel rows)
+__global__ void __launch_bounds__(256) k_explicit_compact(DevProblem P) {
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= P.sp_npanel) return;
+    const int4 pn = __ldg(P.sp_panel + q);
+    const int m6 = pn.z;
+    const uint16_t* stat = P.sp_idx + 8 * (size_t)pn.y;   // header + column map
+    const uint16_t* cmap = stat + 8;
+    const double* src = P.ex_Sown + (size_t)(pn.w >> 6) * EX_TD * EX_TD + (size_t)(6 * (pn.w & 63)) * EX_TD;
+    double* out = P.sp_data + 2 * (size_t)pn.x;
+    double* dst = out + 2;
+    for (int c = lane; c < m6; c += 32) {
+        const int cj = __ldg(cmap + c);
+#pragma unroll
+        for (int r = 0; r < 6; r++) __stcs(dst + r * m6 + c, __ldcs(src + (size_t)r * EX_TD + cj));
+    }
+    // 16-byte units of the static part: the header in front, the map behind the values
+    const uint4* st4 = reinterpret_cast<const uint4*>(stat);
+    if (lane == 0) reinterpret_cast<uint4*>(out)[0] = __ldg(st4);
+    uint4* map_out = reinterpret_cast<uint4*>(dst + 6 * m6);
+    for (int k = lane; k < (2 * m6 + 15) / 16; k += 32) map_out[k] = __ldg(st4 + 1 + k);
+}
+void launch_explicit_compact(const DevProblem& P, cudaStream_t st) {
+    if (!P.ex_on || !P.sp_on) return;
+    k_explicit_compact<<<cdiv(P.sp_npanel * 32, 256), 256, 0, st>>>(P);
+}
+
 // ---------------------------------------------------------------------------
 // mat-vec on the tiles.  CTA = (tile, EX_CHUNK-row chunk), EX_MVW warps x 16 rows.  Lane l owns the columns l + 32 k
 // (k < 12) of the tile: every load instruction of a warp is one coalesced 256-byte run of a tile row, read once

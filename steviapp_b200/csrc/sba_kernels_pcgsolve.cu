@@ -44,16 +44,25 @@ constexpr int PS_STAGES = 2 * PS_CWARPS;        // ring stages, two per consumer
 constexpr int PS_HALF_ROWS = 4;                 // rows per stage
 constexpr uint32_t PS_STAGE_BYTES = PS_HALF_ROWS * EX_TD * sizeof(double);   // 12288
 static_assert(PS_THREADS == PS_CHAINS * PS_ITEM, "fold roles cover the CTA");
+// block-sparse variant (SP): the unit is a PANEL = the non-zero 6x6 blocks of one block row of a tile: 16-byte header
+// {first row, m6}, 6 rows x m6 doubles (m6 <= 384), the 16-bit tile column of every panel column.  Panels have very
+// different sizes (288 B .. 19 KB), so the ring is a BYTE ring: the producer places panel after panel contiguously
+// (wrapping early when one does not fit at the end), one mbarrier pair per in-flight panel (SP_SLOTS of them)
+constexpr int SP_SLOTS = 64;   // a multiple of the consumer warps: a slot belongs to one warp
+constexpr uint32_t SP_RING_BYTES = PS_STAGES * PS_STAGE_BYTES;
+static_assert(SP_RING_BYTES >= 2 * (16 + 6 * EX_TD * 8 + 2 * EX_TD), "two maximal panels fit the ring");
 
 struct PsSmem {
     double ring[PS_STAGES][PS_HALF_ROWS * EX_TD];   // 192 KB
     double col[PS_CWARPS][EX_TD];                   // column partials of the consumer warps of one segment
     double xI[EX_TD];                               // p of the segment's row tile
+    double xJ[EX_TD];                               // p of the segment's column tile (SP only: gathered through the column map)
     double v[PS_CHAINS][PS_ITEM];                   // chain sums of the fold / r of the item
     double sh[33];
     double pq;
     double pqw[PS_CWARPS];
-    unsigned long long full[PS_STAGES], empty[PS_STAGES];
+    unsigned long long full[SP_SLOTS], empty[SP_SLOTS];   // dense: the first PS_STAGES
+    unsigned int poff[SP_SLOTS];                    // SP: byte offset of the slot's panel in the ring
 };
 
 __device__ __forceinline__ uint32_t ps_saddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -85,6 +94,11 @@ __device__ __forceinline__ void ps_bulk_load(void* dst, const void* src, uint32_
 __device__ __forceinline__ void ps_bulk_load_hint(void* dst, const void* src, uint32_t bytes, unsigned long long* bar, uint64_t policy) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  :: "r"(ps_saddr(dst)), "l"(src), "r"(bytes), "r"(ps_saddr(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ long long ps_clock_now() {   // ordered against memory operations (measurement only)
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
+    return t;
 }
 __device__ __forceinline__ void ps_consumer_sync() { asm volatile("bar.sync 1, %0;" :: "n"(32 * PS_CWARPS) : "memory"); }
 
@@ -120,6 +134,7 @@ __device__ __forceinline__ double ps_warp_sum8(const double (&v)[8], int lane) {
     return q;   // total of value (lane >> 2) in every lane
 }
 
+template <bool SP>
 __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters, int pin_hg) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char ps_smem_raw[];
@@ -129,7 +144,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     const int n = 6 * P.Nc;
     const int G = P.xchg_n, me = P.xchg_rank;
     if (tid == 0) {
-        for (int s = 0; s < PS_STAGES; s++) { ps_mbar_init(&sm.full[s], 1); ps_mbar_init(&sm.empty[s], 1); }
+        for (int s = 0; s < SP_SLOTS; s++) { ps_mbar_init(&sm.full[s], 1); ps_mbar_init(&sm.empty[s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // ---- owner role: item b = elements 96 b .. 96 b + 95, thread tid < 96 owns element i
@@ -175,20 +190,27 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     double beta = 0.0;
     int it = 0, cur = 0;
     uint32_t seq = G > 1 ? *P.xchg_ctr : 0u;
-    const int seg0 = P.ps_seg_ptr[b], seg1 = P.ps_seg_ptr[b + 1];
+    const int32_t* seg_tab = SP ? P.sp_seg : P.ps_seg;
+    double* part = SP ? P.sp_part : P.ps_part;
+    const int32_t* fold_ptr = SP ? P.sp_fold_ptr : P.ps_fold_ptr;
+    const int32_t* fold_off = SP ? P.sp_fold_off : P.ps_fold_off;
+    const int seg0 = (SP ? P.sp_seg_ptr : P.ps_seg_ptr)[b], seg1 = (SP ? P.sp_seg_ptr : P.ps_seg_ptr)[b + 1];
     const size_t colbase = (size_t)P.ex_nown * EX_TD;
     // this CTA's run: groups gb0 .. gb0 + ng - 1 of the rank's 8-row groups = one contiguous byte range of the tiles
     int ng = 0;
     const double* run = nullptr;
+    int q_first = 0;   // SP: first panel of the run (ng = number of panels)
     if (seg1 > seg0) {
-        const int4 S0 = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + seg0);
-        run = P.ex_Sown + ((size_t)S0.x * 48 + S0.y) * 8 * EX_TD;
-        for (int sg = seg0; sg < seg1; sg++) { const int4 S = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + sg); ng += S.z - S.y; }
+        const int4 S0 = __ldg(reinterpret_cast<const int4*>(seg_tab) + seg0);
+        if (SP) q_first = S0.y; else run = P.ex_Sown + ((size_t)S0.x * 48 + S0.y) * 8 * EX_TD;
+        for (int sg = seg0; sg < seg1; sg++) { const int4 S = __ldg(reinterpret_cast<const int4*>(seg_tab) + sg); ng += S.z - S.y; }
     }
+    double* const ring_flat = &sm.ring[0][0];
     unsigned int jdone = 0;   // groups streamed in the previous iterations: stage = (2 * group number + half) % 16
     // phase clock of CTA 0 (ns, summed over the iterations): mat-vec, barrier 1, fold + vector part, barrier 2 + scalars
     auto now = [&]() -> long long { long long t = 0; if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
     long long t_m = 0, t_s1 = 0, t_f = 0, t_s2 = 0, t_a = now();
+    long long w_cons = 0, w_comp = 0;   // SP: cycles warp 0 waited for chunks / spent on their panels
 
     while (rz > tol2 * rz0 && rz0 > 0.0 && it < max_iters) {
         const double* p_old = cur ? P.pcg_p2 : P.pcg_p;
@@ -196,7 +218,56 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         // ---- direction of this iteration (owner copy; the mat-vec below rebuilds the same values from z, beta, p_old)
         if (owner) { p_i = ps_dir(z_i, beta, p_i); __stcg(p_new + i, p_i); }
         // ---- M: tile mat-vec over this CTA's run
-        if (producer) {
+        if (producer && SP) {
+            // The descriptors are fetched 32 at a time by the whole warp (next batch in flight while lane 0 issues the current
+            // one); pin_hg = bytes of the run to keep in L2.  All panels of the earlier iterations are consumed (block barrier
+            // at the end of M), so every iteration starts with an empty ring.
+            uint64_t pol_keep, pol_stream;
+            asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+            unsigned int bytes_done = 0, tailH = jdone;
+            uint32_t head = 0, tail = 0;
+            volatile unsigned int* poff = sm.poff;
+            // lane 0 alone (no warp-level reconvergence between two copies: a shuffle after the bulk copy was measured to hold
+            // the next copy back until the previous one had landed); the descriptors of the next 8 panels are in registers
+            if (lane == 0) {
+                constexpr int PF = 8;
+                int4 d[PF];
+#pragma unroll
+                for (int j = 0; j < PF; j++) d[j] = j < ng ? __ldg(P.sp_chunk + q_first + j) : make_int4(0, 0, 0, 0);
+                for (int base = 0; base < ng; base += PF) {
+#pragma unroll
+                    for (int j = 0; j < PF; j++) {
+                        if (base + j >= ng) break;
+                        const int dx = d[j].x;
+                        const uint32_t B = (uint32_t)d[j].y;   // a multiple of 128: panels start on 128-byte boundaries (stream and ring)
+                        if (base + j + PF < ng) d[j] = __ldg(P.sp_chunk + q_first + base + j + PF);
+                        const unsigned int H = jdone + base + j, slot = H % SP_SLOTS;
+                        auto free_oldest = [&]() {   // panels are released in any order by the warps, reclaimed in order here
+                            ps_mbar_wait(&sm.empty[tailH % SP_SLOTS], (tailH / SP_SLOTS) & 1u);
+                            tailH++;
+                            tail = tailH == H ? head : poff[tailH % SP_SLOTS];
+                        };
+                        while ((int)(H - tailH) >= SP_SLOTS) free_oldest();   // the slot's previous panel is consumed
+                        uint32_t at;
+                        while (true) {
+                            if (tailH == H) { head = tail = 0; at = 0; break; }
+                            if (head >= tail) {
+                                if (head + B <= SP_RING_BYTES) { at = head; break; }
+                                if (B < tail) { at = 0; break; }             // strict: head == tail means empty
+                            } else if (head + B < tail) { at = head; break; }
+                            free_oldest();
+                        }
+                        head = at + B;
+                        poff[slot] = at;
+                        ps_mbar_expect_tx(&sm.full[slot], B);
+                        ps_bulk_load_hint(reinterpret_cast<unsigned char*>(ring_flat) + at, reinterpret_cast<const unsigned char*>(P.sp_data) + 16 * (size_t)(unsigned int)dx,
+                                          B, &sm.full[slot], bytes_done < (unsigned int)pin_hg ? pol_keep : pol_stream);
+                        bytes_done += B;
+                    }
+                }
+            }
+        } else if (producer) {
             if (lane == 0) {
                 // the first pin_hg half groups of every run are loaded evict_last: S does not change during the solve, so that
                 // share of the tiles (sized to the L2 by the host) is served from L2 from the second CG iteration on; the rest
@@ -204,6 +275,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                 uint64_t pol_keep, pol_stream;
                 asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
                 asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+                if constexpr (SP) { } else
                 for (unsigned int h = 0; h < 2u * ng; h++) {
                     const unsigned int H = 2u * jdone + h, s = H % PS_STAGES, use = H / PS_STAGES;
                     if (use > 0) ps_mbar_wait(&sm.empty[s], (use - 1) & 1u);   // the owner warp has released the previous contents
@@ -216,10 +288,77 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
             double pq_lane = 0.0;
             unsigned int jseg = jdone;   // number of the first group of the segment
             for (int sg = seg0; sg < seg1; sg++) {
-                const int4 S = __ldg(reinterpret_cast<const int4*>(P.ps_seg) + sg);   // local tile, first group, end group
+                const int4 S = __ldg(reinterpret_cast<const int4*>(seg_tab) + sg);   // local tile, first group, end group (SP: panels)
                 const int tile = S.x, g0 = S.y, g1 = S.z;
                 const int I = __ldg(P.ex_tile_I + P.ex_own0 + tile), J = __ldg(P.ex_tile_J + P.ex_own0 + tile);
                 ps_consumer_sync();   // xI / col of the previous segment are free
+                if constexpr (SP) {
+                    for (int r = tid; r < EX_TD; r += 32 * PS_CWARPS) {
+                        const int gi = EX_TD * I + r, gj = EX_TD * J + r;
+                        sm.xI[r] = gi < n ? ps_dir(__ldcg(P.pcg_z + gi), beta, __ldcg(p_old + gi)) : 0.0;
+                        sm.xJ[r] = gj < n ? ps_dir(__ldcg(P.pcg_z + gj), beta, __ldcg(p_old + gj)) : 0.0;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 12; k++) sm.col[warp][lane + 32 * k] = 0.0;
+                    ps_consumer_sync();
+                    // panels of the segment whose running number is = warp (mod 8); a warp's column sums live in its row of sm.col
+                    const unsigned int first = (warp + PS_CWARPS - (jseg % PS_CWARPS)) % PS_CWARPS;
+                    double* colw = sm.col[warp];
+                    for (unsigned int o = first; o < (unsigned int)(g1 - g0); o += PS_CWARPS) {
+                        // slot H % 64 is always consumed by warp H % 8, in order: the warp is never more than one phase ahead of
+                        // the slot's barrier, so the parity wait is unambiguous
+                        const unsigned int H = jseg + o, s = H % SP_SLOTS;
+                        const long long w0 = ps_clock_now();
+                        ps_mbar_wait(&sm.full[s], (H / SP_SLOTS) & 1u);
+                        const uint32_t at = *reinterpret_cast<volatile unsigned int*>(&sm.poff[s]);   // written before the producer's arrive (release) on full[s]
+                        const long long w1 = ps_clock_now();
+                        w_cons += w1 - w0;
+
+                        const unsigned char* pbase = reinterpret_cast<const unsigned char*>(ring_flat) + at;
+                        const int np = reinterpret_cast<const uint16_t*>(pbase)[2];   // panels of the chunk
+                        for (int pk = 0; pk < np; pk++) {
+                        const int row0 = reinterpret_cast<const uint16_t*>(pbase)[0], m6 = reinterpret_cast<const uint16_t*>(pbase)[1];
+                        const double* buf = reinterpret_cast<const double*>(pbase + 16);
+                        const uint16_t* cmap = reinterpret_cast<const uint16_t*>(buf + 6 * m6);
+                        double xi[6], racc[6];
+#pragma unroll
+                        for (int r = 0; r < 6; r++) { xi[r] = sm.xI[row0 + r]; racc[r] = 0.0; }
+                        int c = lane;
+                        for (; c + 32 < m6; c += 64) {   // two columns per lane in flight (distinct columns: no aliasing in colw)
+                            const int ca = cmap[c], cb = cmap[c + 32];
+                            const double xa = sm.xJ[ca], xb = sm.xJ[cb];
+                            const double wa = colw[ca], wb = colw[cb];
+                            double va[6], vb[6];
+#pragma unroll
+                            for (int r = 0; r < 6; r++) { va[r] = buf[r * m6 + c]; vb[r] = buf[r * m6 + c + 32]; }
+#pragma unroll
+                            for (int r = 0; r < 6; r++) { racc[r] += va[r] * xa; racc[r] += vb[r] * xb; }
+                            colw[ca] = wa + ((va[0] * xi[0] + va[1] * xi[1] + va[2] * xi[2]) + (va[3] * xi[3] + va[4] * xi[4] + va[5] * xi[5]));
+                            colw[cb] = wb + ((vb[0] * xi[0] + vb[1] * xi[1] + vb[2] * xi[2]) + (vb[3] * xi[3] + vb[4] * xi[4] + vb[5] * xi[5]));
+                        }
+                        if (c < m6) {
+                            const int ca = cmap[c];
+                            const double xa = sm.xJ[ca], wa = colw[ca];
+                            double va[6];
+#pragma unroll
+                            for (int r = 0; r < 6; r++) va[r] = buf[r * m6 + c];
+#pragma unroll
+                            for (int r = 0; r < 6; r++) racc[r] += va[r] * xa;
+                            colw[ca] = wa + ((va[0] * xi[0] + va[1] * xi[1] + va[2] * xi[2]) + (va[3] * xi[3] + va[4] * xi[4] + va[5] * xi[5]));
+                        }
+                        int j6;
+                        const double s6 = warp_sum6(racc, lane, &j6);
+                        if ((lane & 3) == 0 && j6 < 6) {
+                            __stcg(part + (size_t)tile * EX_TD + row0 + j6, s6);
+                            pq_lane += sm.xI[row0 + j6] * s6;
+                        }
+                        pbase += (16 + 50 * m6 + 127) & ~127;
+                        }
+                        __syncwarp();
+                        if (lane == 0) ps_mbar_arrive(&sm.empty[s]);
+                        w_comp += ps_clock_now() - w1;
+                    }
+                } else {
                 for (int r = 8 * g0 + tid; r < 8 * g1; r += 32 * PS_CWARPS) {
                     const int gi = EX_TD * I + r;
                     sm.xI[r] = gi < n ? ps_dir(__ldcg(P.pcg_z + gi), beta, __ldcg(p_old + gi)) : 0.0;
@@ -262,18 +401,19 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                     const double s8 = ps_warp_sum8(racc, lane);
                     if ((lane & 3) == 0) {
                         const int r = row0 + (lane >> 2);
-                        __stcg(P.ps_part + (size_t)tile * EX_TD + r, s8);
+                        __stcg(part + (size_t)tile * EX_TD + r, s8);
                         pq_lane += sm.xI[r] * s8;
                     }
                 }
 #pragma unroll
                 for (int k = 0; k < 12; k++) sm.col[warp][lane + 32 * k] = col[k];
+                }
                 ps_consumer_sync();
                 for (int c = tid; c < EX_TD; c += 32 * PS_CWARPS) {
                     double acc = sm.col[0][c];
 #pragma unroll
                     for (int w = 1; w < PS_CWARPS; w++) acc += sm.col[w][c];   // warp order: fixed
-                    __stcg(P.ps_part + colbase + (size_t)sg * EX_TD + c, acc);
+                    __stcg(part + colbase + (size_t)sg * EX_TD + c, acc);
                 }
                 jseg += (unsigned int)(g1 - g0);
             }
@@ -296,19 +436,19 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         // ---- F: q of the item (fold of the partials that touch its camera tile), alpha, x, r, z, item part of r.z
         if (has_item) {
             const int K = (b * PS_ITEM) / EX_TD;
-            const int m0 = __ldg(P.ps_fold_ptr + K), m1 = __ldg(P.ps_fold_ptr + K + 1);
+            const int m0 = __ldg(fold_ptr + K), m1 = __ldg(fold_ptr + K + 1);
             {   // chain ch sums the entries m0 + ch, m0 + ch + 3, ... in list order
-                const double* base = P.ps_part + (b * PS_ITEM - K * EX_TD + e);
+                const double* base = part + (b * PS_ITEM - K * EX_TD + e);
                 double acc = 0.0;
                 int m = m0 + ch;
                 for (; m + 15 * PS_CHAINS < m1; m += 16 * PS_CHAINS) {   // 16 loads in flight
                     double v[16];
 #pragma unroll
-                    for (int k = 0; k < 16; k++) v[k] = __ldcg(base + __ldg(P.ps_fold_off + m + PS_CHAINS * k));
+                    for (int k = 0; k < 16; k++) v[k] = __ldcg(base + __ldg(fold_off + m + PS_CHAINS * k));
 #pragma unroll
                     for (int k = 0; k < 16; k++) acc += v[k];
                 }
-                for (; m < m1; m += PS_CHAINS) acc += __ldcg(base + __ldg(P.ps_fold_off + m));
+                for (; m < m1; m += PS_CHAINS) acc += __ldcg(base + __ldg(fold_off + m));
                 sm.v[ch][e] = acc;
             }
             double pq = ps_fold(P.ps_pq, gridDim.x, sm.sh);   // this rank's p^T S p / 2 (barriers inside: sm.v is visible below)
@@ -377,6 +517,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         unsigned int smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         P.ps_clock[4 + 2 * b] = (double)t_m; P.ps_clock[5 + 2 * b] = (double)smid;
+        if (SP) { P.ps_clock[4 + 2 * gridDim.x + 2 * b] = (double)w_cons; P.ps_clock[5 + 2 * gridDim.x + 2 * b] = (double)w_comp; }
     }
 }
 
@@ -390,8 +531,10 @@ static int ps_grid_blocks() {
         cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         blocks = 0;
         if (coop && smem_max >= (int)sizeof(PsSmem) &&
-            cudaFuncSetAttribute(k_pcg_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsSmem)) == cudaSuccess &&
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve, PS_THREADS, sizeof(PsSmem)) == cudaSuccess && per_sm >= 1)
+            cudaFuncSetAttribute(k_pcg_solve<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsSmem)) == cudaSuccess &&
+            cudaFuncSetAttribute(k_pcg_solve<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PsSmem)) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve<false>, PS_THREADS, sizeof(PsSmem)) == cudaSuccess && per_sm >= 1 &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg_solve<true>, PS_THREADS, sizeof(PsSmem)) == cudaSuccess && per_sm >= 1)
             blocks = sms;
         cudaGetLastError();
     }
@@ -407,8 +550,9 @@ bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStrea
     // as the same number of leading 12 KB half groups of every CTA's run
     static const double l2_mb = std::getenv("SBA_PS_L2_MB") ? std::atof(std::getenv("SBA_PS_L2_MB")) : 80.0;
     int pin_hg = (int)(l2_mb * 1e6 / ((double)P.ps_grid * PS_STAGE_BYTES));
+    if (P.sp_on) pin_hg = (int)(l2_mb * 1e6 / (double)P.ps_grid);   // bytes of every run
     void* args[] = {&Pc, &tol2, &max_iters, &pin_hg};
-    return cudaLaunchCooperativeKernel((void*)k_pcg_solve, dim3(P.ps_grid), dim3(PS_THREADS), args, sizeof(PsSmem), st) == cudaSuccess;
+    return cudaLaunchCooperativeKernel(P.sp_on ? (void*)k_pcg_solve<true> : (void*)k_pcg_solve<false>, dim3(P.ps_grid), dim3(PS_THREADS), args, sizeof(PsSmem), st) == cudaSuccess;
 }
 
 }  // namespace sba

@@ -205,6 +205,12 @@ class SBASolver:
         self._check(self._lib.sba_explicit_shard(self._h, *[C.byref(x) for x in v]))
         return dict(zip(("first_tile", "n_own", "peer_exchange", "persistent_pcg"), [x.value for x in v]))
 
+    def explicit_sparse_info(self):
+        """Block-sparse copy of the tiles read by the persistent PCG kernel (panels of non-zero 6x6 blocks, chunks = bulk copies)."""
+        v = [C.c_int32(), C.c_int32(), C.c_int32(), C.c_int64(), C.c_int64()]
+        self._check(self._lib.sba_explicit_sparse_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("enabled", "n_panels", "n_chunks", "n_blocks", "stream_bytes"), [x.value for x in v]))
+
     def explicit_dense(self):
         """The reduced camera system of the last LM iteration as a dense symmetric matrix (6 n_cams)^2 and its rhs
         (inspection hook over sba_explicit_tiles; small problems / studies only)."""
