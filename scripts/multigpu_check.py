@@ -20,7 +20,11 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 fixed = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
-sc = synthetic.make_scene(shape)
+if shape.startswith("cams"):   # e.g. cams300: several tiles, band structure
+    n = int(shape[4:])
+    sc = synthetic.make_scene(None, n_cams=n, n_pts=100 * n, n_obs=500 * n, seed=7)
+else:
+    sc = synthetic.make_scene(shape)
 sh = synthetic.shard_scene(sc, rank, world)
 
 r1 = None
@@ -42,7 +46,7 @@ for name, op_mode, peer in (("explicit+peer", 3, "1"), ("explicit+nccl", 3, "0")
     s.comm_init(rank, world, uid[0])
     raxis, t, pts = synthetic.load_into(s, sh)
     s.finalize()
-    info = dict(s.explicit_info(), **s.explicit_shard())
+    info = dict(s.explicit_info(), **s.explicit_shard(), sparse=s.explicit_sparse_info()["enabled"])
     r = s.solve(max_iterations=iters)
     ra = (raxis.copy(), t.copy(), pts.copy())
     out = {"rank": rank, "shard_obs": sh["n_obs"], "cost_history": r["cost_history"], "pcg": r["pcg_iters_history"],

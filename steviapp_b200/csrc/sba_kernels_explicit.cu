@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) k_explicit_compact(DevProblem P) {
     for (int k = lane; k < (2 * m6 + 15) / 16; k += 32) map_out[k] = __ldg(st4 + 1 + k);
 }
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st) {
-    if (!P.ex_on || !P.sp_on) return;
+    if (!P.ex_on || !P.ps_on || !P.sp_on) return;
     k_explicit_compact<<<cdiv(P.sp_npanel * 32, 256), 256, 0, st>>>(P);
 }
 

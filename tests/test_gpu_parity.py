@@ -386,6 +386,23 @@ def test_two_gpu_sharded_solve_matches_single_gpu():
     assert res["modes"][0]["info"][0]["peer_exchange"] == 1 and res["modes"][0]["info"][0]["persistent_pcg"] == 1
 
 
+def test_two_gpu_block_sparse_panels():
+    """2 GPUs, several tiles per rank, block-sparse panels forced on: the block structure is the union over the ranks (a rank
+    compacts the tiles it owns, whose blocks come from every rank's points); same 1e-8 / bit-identical-cameras gates."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29534", os.path.join(root, "scripts", "multigpu_check.py"), "cams300", "3", "explicit+peer"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=280, env=dict(os.environ, SBA_PS_SPARSE="1"))
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    res = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
+    assert res["ok"] and all(i["sparse"] == 1 and i["persistent_pcg"] == 1 for i in res["modes"][0]["info"])
+
+
 def test_venice_scale_explicit_tiles_against_implicit_operator(monkeypatch):
     """Full BASELINE size: the explicit reduced camera system (406 dense tiles built from 11.6 M point-pair contributions) and
     the implicit operator (two passes over the 5 M observations) are independent code paths for the same S; they must agree
