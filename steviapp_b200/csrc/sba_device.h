@@ -138,10 +138,11 @@ struct DevProblem {
     int32_t sp_nchunk;
     int64_t sp_bytes;     // bytes of the panel stream (what one CG iteration reads)
     int64_t sp_nblocks;   // 6x6 blocks kept (structurally non-zero, upper triangle + diagonal)
-    int4* sp_chunk;       // per chunk = consecutive panels of a tile that travel as one bulk copy: x stream offset / 16, y bytes, z panels, w first panel
+    int4* sp_chunk;       // per chunk = consecutive panels of a tile that travel as one bulk copy: x stream offset / 16, y bytes, z directory offset / 16 in sp_idx, w directory bytes
     int4* sp_panel;       // per panel: x stream offset and y map offset in 16-byte units, z m6 = 6 * non-zero blocks, w tile * 64 + block row
-    double* sp_data;      // the stream the CG iterations read, panel after panel: 16-byte header {first row in the tile, m6}, 6 rows x m6 doubles, column map
-    uint16_t* sp_idx;     // static part, panel after panel: the header, then the tile column of every panel column (padded to 16 B)
+    double* sp_data;      // the stream the CG iterations read, chunk after chunk: directory {panels, first panel mod 8, offset / 128 of every panel}, then per
+                          // panel a 16-byte header {first row in the tile, m6}, 6 rows x m6 doubles, the column map; everything on 128-byte boundaries
+    uint16_t* sp_idx;     // static part in the same order: directories, headers and column maps
     int32_t* sp_seg_ptr;  // ps_grid + 1
     int32_t* sp_seg;      // 4 per segment: local tile, first chunk, end chunk, pad
     double* sp_part;      // ex_nown * 384 row partials, then sp_nseg * 384 column partials
@@ -254,6 +255,7 @@ void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st
 void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t st);
 // explicit reduced camera system
 void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> off-diagonal blocks of ex_S (needs Hinv of this LM iteration)
+void launch_explicit_sparse_dirs(const DevProblem& P, cudaStream_t st);   // chunk directories -> panel stream (once, at finalize)
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st);   // dense tiles -> block-sparse panels (sp_on)
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st);      // diagonal blocks of the owned tiles (needs Hcc, Sd, lam_c; multi-GPU: after the reduce-scatter)
 void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg = 0, double tol2 = 0.0,

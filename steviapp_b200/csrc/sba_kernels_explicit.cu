@@ -206,6 +206,18 @@ __global__ void __launch_bounds__(256) k_explicit_compact(DevProblem P) {
     uint4* map_out = reinterpret_cast<uint4*>(dst + 6 * m6);
     for (int k = lane; k < (2 * m6 + 15) / 16; k += 32) map_out[k] = __ldg(st4 + 1 + k);
 }
+__global__ void __launch_bounds__(256) k_explicit_sparse_dirs(DevProblem P) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (c >= P.sp_nchunk) return;
+    const int4 ch = __ldg(P.sp_chunk + c);
+    const uint4* src = reinterpret_cast<const uint4*>(P.sp_idx + 8 * (size_t)ch.z);
+    uint4* dst = reinterpret_cast<uint4*>(P.sp_data + 2 * (size_t)ch.x);
+    for (int k = lane; k < ch.w / 16; k += 32) dst[k] = __ldg(src + k);
+}
+void launch_explicit_sparse_dirs(const DevProblem& P, cudaStream_t st) {
+    if (!P.sp_on || !P.sp_nchunk) return;
+    k_explicit_sparse_dirs<<<cdiv(P.sp_nchunk * 32, 256), 256, 0, st>>>(P);
+}
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on || !P.ps_on || !P.sp_on) return;
     k_explicit_compact<<<cdiv(P.sp_npanel * 32, 256), 256, 0, st>>>(P);

@@ -44,13 +44,18 @@ constexpr int PS_STAGES = 2 * PS_CWARPS;        // ring stages, two per consumer
 constexpr int PS_HALF_ROWS = 4;                 // rows per stage
 constexpr uint32_t PS_STAGE_BYTES = PS_HALF_ROWS * EX_TD * sizeof(double);   // 12288
 static_assert(PS_THREADS == PS_CHAINS * PS_ITEM, "fold roles cover the CTA");
-// block-sparse variant (SP): the unit is a PANEL = the non-zero 6x6 blocks of one block row of a tile: 16-byte header
-// {first row, m6}, 6 rows x m6 doubles (m6 <= 384), the 16-bit tile column of every panel column.  Panels have very
-// different sizes (288 B .. 19 KB), so the ring is a BYTE ring: the producer places panel after panel contiguously
-// (wrapping early when one does not fit at the end), one mbarrier pair per in-flight panel (SP_SLOTS of them)
-constexpr int SP_SLOTS = 64;   // a multiple of the consumer warps: a slot belongs to one warp
+// block-sparse variant (SP): the unit of work is a PANEL = the non-zero 6x6 blocks of one block row of a tile: 16-byte
+// header {first row, m6}, 6 rows x m6 doubles (m6 <= 384), the 16-bit tile column of every panel column.  The unit of
+// transfer is a CHUNK = directory + consecutive panels of one tile, <= 40 KB, ONE bulk copy (the producer lane needs
+// ~0.3 us per copy whatever its size: with one copy per panel it was the bound).  Chunks have very different sizes, so the
+// ring is a BYTE ring: the producer places chunk after chunk contiguously (wrapping early when one does not fit at the
+// end), one mbarrier pair per in-flight chunk (SP_SLOTS of them).  EVERY consumer warp visits every chunk in order (the
+// panels of a chunk are dealt round-robin to the warps, by panel number mod 8) and arrives on its empty barrier (count 8):
+// no warp can be more than one phase ahead of a slot's barrier, so the parity waits are unambiguous.
+constexpr int SP_SLOTS = PS_STAGES;
 constexpr uint32_t SP_RING_BYTES = PS_STAGES * PS_STAGE_BYTES;
-static_assert(SP_RING_BYTES >= 2 * (16 + 6 * EX_TD * 8 + 2 * EX_TD), "two maximal panels fit the ring");
+constexpr uint32_t SP_CHUNK_MAX = 40960;   // sba_solver_explicit.inc builds the chunks
+static_assert(SP_RING_BYTES >= 4 * SP_CHUNK_MAX, "four maximal chunks fit the ring");
 
 struct PsSmem {
     double ring[PS_STAGES][PS_HALF_ROWS * EX_TD];   // 192 KB
@@ -61,8 +66,8 @@ struct PsSmem {
     double sh[33];
     double pq;
     double pqw[PS_CWARPS];
-    unsigned long long full[SP_SLOTS], empty[SP_SLOTS];   // dense: the first PS_STAGES
-    unsigned int poff[SP_SLOTS];                    // SP: byte offset of the slot's panel in the ring
+    unsigned long long full[PS_STAGES], empty[PS_STAGES];
+    unsigned int poff[SP_SLOTS];                    // SP: byte offset of the slot's chunk in the ring
 };
 
 __device__ __forceinline__ uint32_t ps_saddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -144,7 +149,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     const int n = 6 * P.Nc;
     const int G = P.xchg_n, me = P.xchg_rank;
     if (tid == 0) {
-        for (int s = 0; s < SP_SLOTS; s++) { ps_mbar_init(&sm.full[s], 1); ps_mbar_init(&sm.empty[s], 1); }
+        for (int s = 0; s < PS_STAGES; s++) { ps_mbar_init(&sm.full[s], 1); ps_mbar_init(&sm.empty[s], SP ? PS_CWARPS : 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // ---- owner role: item b = elements 96 b .. 96 b + 95, thread tid < 96 owns element i
@@ -301,22 +306,21 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
 #pragma unroll
                     for (int k = 0; k < 12; k++) sm.col[warp][lane + 32 * k] = 0.0;
                     ps_consumer_sync();
-                    // panels of the segment whose running number is = warp (mod 8); a warp's column sums live in its row of sm.col
-                    const unsigned int first = (warp + PS_CWARPS - (jseg % PS_CWARPS)) % PS_CWARPS;
+                    // every warp visits every chunk of the segment; of its panels it takes those whose number is = warp (mod 8);
+                    // a warp's column sums live in its row of sm.col
                     double* colw = sm.col[warp];
-                    for (unsigned int o = first; o < (unsigned int)(g1 - g0); o += PS_CWARPS) {
-                        // slot H % 64 is always consumed by warp H % 8, in order: the warp is never more than one phase ahead of
-                        // the slot's barrier, so the parity wait is unambiguous
+                    for (unsigned int o = 0; o < (unsigned int)(g1 - g0); o++) {
                         const unsigned int H = jseg + o, s = H % SP_SLOTS;
                         const long long w0 = ps_clock_now();
                         ps_mbar_wait(&sm.full[s], (H / SP_SLOTS) & 1u);
                         const uint32_t at = *reinterpret_cast<volatile unsigned int*>(&sm.poff[s]);   // written before the producer's arrive (release) on full[s]
                         const long long w1 = ps_clock_now();
                         w_cons += w1 - w0;
-
-                        const unsigned char* pbase = reinterpret_cast<const unsigned char*>(ring_flat) + at;
-                        const int np = reinterpret_cast<const uint16_t*>(pbase)[2];   // panels of the chunk
-                        for (int pk = 0; pk < np; pk++) {
+                        const unsigned char* cbase = reinterpret_cast<const unsigned char*>(ring_flat) + at;
+                        const uint16_t* dir = reinterpret_cast<const uint16_t*>(cbase);
+                        const int np = dir[0];
+                        for (int pk = (warp + PS_CWARPS - dir[1]) % PS_CWARPS; pk < np; pk += PS_CWARPS) {
+                        const unsigned char* pbase = cbase + 128u * dir[2 + pk];
                         const int row0 = reinterpret_cast<const uint16_t*>(pbase)[0], m6 = reinterpret_cast<const uint16_t*>(pbase)[1];
                         const double* buf = reinterpret_cast<const double*>(pbase + 16);
                         const uint16_t* cmap = reinterpret_cast<const uint16_t*>(buf + 6 * m6);
@@ -352,7 +356,6 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                             __stcg(part + (size_t)tile * EX_TD + row0 + j6, s6);
                             pq_lane += sm.xI[row0 + j6] * s6;
                         }
-                        pbase += (16 + 50 * m6 + 127) & ~127;
                         }
                         __syncwarp();
                         if (lane == 0) ps_mbar_arrive(&sm.empty[s]);
