@@ -54,8 +54,8 @@ static_assert(PS_THREADS == PS_CHAINS * PS_ITEM, "fold roles cover the CTA");
 // no warp can be more than one phase ahead of a slot's barrier, so the parity waits are unambiguous.
 constexpr int SP_SLOTS = PS_STAGES;
 constexpr uint32_t SP_RING_BYTES = PS_STAGES * PS_STAGE_BYTES;
-constexpr uint32_t SP_CHUNK_MAX = 40960;   // sba_solver_explicit.inc builds the chunks
-static_assert(SP_RING_BYTES >= 4 * SP_CHUNK_MAX, "four maximal chunks fit the ring");
+constexpr uint32_t SP_CHUNK_MAX = 65536;   // upper bound of what sba_solver_explicit.inc builds (default 40 KB)
+static_assert(SP_RING_BYTES >= 3 * SP_CHUNK_MAX, "three maximal chunks fit the ring");
 
 struct PsSmem {
     double ring[PS_STAGES][PS_HALF_ROWS * EX_TD];   // 192 KB
@@ -140,7 +140,7 @@ __device__ __forceinline__ double ps_warp_sum8(const double (&v)[8], int lane) {
 }
 
 template <bool SP>
-__global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters, int pin_hg) {
+__global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, double tol2, int max_iters, int pin_hg, int pin_f16, int ps_mode) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char ps_smem_raw[];
     PsSmem& sm = *reinterpret_cast<PsSmem*>(ps_smem_raw);
@@ -212,6 +212,50 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     }
     double* const ring_flat = &sm.ring[0][0];
     unsigned int jdone = 0;   // groups streamed in the previous iterations: stage = (2 * group number + half) % 16
+    // ---- ring prefetch (ps_mode bit 0): S does not change during the solve and the ring is empty at the end of every mat-vec
+    // (block barrier), so the producer warp refills it with the FIRST chunks / stages of the run right away -- one copy per
+    // lane, positions static -- and the copies land while the CTA sits in the two grid barriers and the fold, when DRAM is
+    // otherwise idle.  The producer loop of the next iteration starts behind them.  ps_mode bit 1: the L2-resident share
+    // (evict_last) is spread evenly over the rest of the run (pin_f16 / 65536 of its bytes) instead of leading it, so that
+    // L2 hits and DRAM streams overlap in time in every CTA.
+    uint64_t pol_keep, pol_stream;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+    const bool do_prefetch = ps_mode & 1, do_interleave = ps_mode & 2;
+    int npre = 0;
+    uint32_t pre_at = 0, pre_B = 0, pre_total = 0;
+    int pre_dx = 0;
+    if (producer && do_prefetch) {
+        if constexpr (SP) {
+            const bool cand = lane < ng && lane < SP_SLOTS;
+            const int4 dsc = cand ? __ldg(P.sp_chunk + q_first + lane) : make_int4(0, 0, 0, 0);
+            uint32_t incl = (uint32_t)dsc.y;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
+            npre = __popc(__ballot_sync(FULL, cand && incl <= SP_RING_BYTES));   // a prefix of the lanes: the sums grow
+            pre_B = (uint32_t)dsc.y; pre_at = incl - pre_B; pre_dx = dsc.x;
+            pre_total = npre > 0 ? __shfl_sync(FULL, incl, npre - 1) : 0u;
+        } else {
+            npre = min(PS_STAGES, 2 * ng);
+        }
+    }
+    auto prefetch = [&](unsigned int jbase) {   // producer warp, ring empty
+        if (lane < npre) {
+            if constexpr (SP) {
+                const unsigned int H = jbase + lane, slot = H % SP_SLOTS;
+                *reinterpret_cast<volatile unsigned int*>(&sm.poff[slot]) = pre_at;
+                ps_mbar_expect_tx(&sm.full[slot], pre_B);
+                ps_bulk_load_hint(reinterpret_cast<unsigned char*>(ring_flat) + pre_at,
+                                  reinterpret_cast<const unsigned char*>(P.sp_data) + 16 * (size_t)(unsigned int)pre_dx, pre_B, &sm.full[slot], pol_stream);
+            } else {
+                const unsigned int H = 2u * jbase + lane, s = H % PS_STAGES;
+                ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
+                ps_bulk_load_hint(sm.ring[s], run + (size_t)lane * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s], pol_stream);
+            }
+        }
+        __syncwarp();
+    };
+    if (producer && npre > 0) prefetch(0u);
     // phase clock of CTA 0 (ns, summed over the iterations): mat-vec, barrier 1, fold + vector part, barrier 2 + scalars
     auto now = [&]() -> long long { long long t = 0; if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
     long long t_m = 0, t_s1 = 0, t_f = 0, t_s2 = 0, t_a = now();
@@ -227,11 +271,10 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
             // The descriptors are fetched 32 at a time by the whole warp (next batch in flight while lane 0 issues the current
             // one); pin_hg = bytes of the run to keep in L2.  All panels of the earlier iterations are consumed (block barrier
             // at the end of M), so every iteration starts with an empty ring.
-            uint64_t pol_keep, pol_stream;
-            asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
-            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+            // With the ring prefetch the first npre chunks are already in flight (oldest at offset 0, head behind the last).
             unsigned int bytes_done = 0, tailH = jdone;
-            uint32_t head = 0, tail = 0;
+            uint32_t head = pre_total, tail = 0;
+            unsigned long long credit = 0;   // interleaved L2 share: a chunk is kept when the credit covers it
             volatile unsigned int* poff = sm.poff;
             // lane 0 alone (no warp-level reconvergence between two copies: a shuffle after the bulk copy was measured to hold
             // the next copy back until the previous one had landed); the descriptors of the next 8 panels are in registers
@@ -239,8 +282,8 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                 constexpr int PF = 8;
                 int4 d[PF];
 #pragma unroll
-                for (int j = 0; j < PF; j++) d[j] = j < ng ? __ldg(P.sp_chunk + q_first + j) : make_int4(0, 0, 0, 0);
-                for (int base = 0; base < ng; base += PF) {
+                for (int j = 0; j < PF; j++) d[j] = npre + j < ng ? __ldg(P.sp_chunk + q_first + npre + j) : make_int4(0, 0, 0, 0);
+                for (int base = npre; base < ng; base += PF) {
 #pragma unroll
                     for (int j = 0; j < PF; j++) {
                         if (base + j >= ng) break;
@@ -266,8 +309,14 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                         head = at + B;
                         poff[slot] = at;
                         ps_mbar_expect_tx(&sm.full[slot], B);
+                        bool keep = bytes_done < (unsigned int)pin_hg;
+                        if (do_interleave) {
+                            credit += (unsigned long long)B * (unsigned int)pin_f16;
+                            keep = credit >= ((unsigned long long)B << 16);
+                            if (keep) credit -= (unsigned long long)B << 16;
+                        }
                         ps_bulk_load_hint(reinterpret_cast<unsigned char*>(ring_flat) + at, reinterpret_cast<const unsigned char*>(P.sp_data) + 16 * (size_t)(unsigned int)dx,
-                                          B, &sm.full[slot], bytes_done < (unsigned int)pin_hg ? pol_keep : pol_stream);
+                                          B, &sm.full[slot], keep ? pol_keep : pol_stream);
                         bytes_done += B;
                     }
                 }
@@ -277,16 +326,17 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                 // the first pin_hg half groups of every run are loaded evict_last: S does not change during the solve, so that
                 // share of the tiles (sized to the L2 by the host) is served from L2 from the second CG iteration on; the rest
                 // streams through evict_first and cannot push it out
-                uint64_t pol_keep, pol_stream;
-                asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
-                asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
+                // (ring prefetch: the first npre stages are already in flight; interleave: every stage whose number crosses a
+                // multiple of 65536 / pin_f16 is kept instead of the leading pin_hg ones)
                 if constexpr (SP) { } else
-                for (unsigned int h = 0; h < 2u * ng; h++) {
+                for (unsigned int h = (unsigned int)npre; h < 2u * ng; h++) {
                     const unsigned int H = 2u * jdone + h, s = H % PS_STAGES, use = H / PS_STAGES;
                     if (use > 0) ps_mbar_wait(&sm.empty[s], (use - 1) & 1u);   // the owner warp has released the previous contents
                     ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
-                    ps_bulk_load_hint(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s],
-                                      (int)h < pin_hg ? pol_keep : pol_stream);
+                    const unsigned int hh = h - (unsigned int)npre;
+                    const bool keep = do_interleave ? (((unsigned long long)(hh + 1) * (unsigned int)pin_f16) >> 16) != (((unsigned long long)hh * (unsigned int)pin_f16) >> 16)
+                                                    : (int)h < pin_hg;
+                    ps_bulk_load_hint(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s], keep ? pol_keep : pol_stream);
                 }
             }
         } else {
@@ -328,7 +378,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
 #pragma unroll
                         for (int r = 0; r < 6; r++) { xi[r] = sm.xI[row0 + r]; racc[r] = 0.0; }
                         int c = lane;
-                        for (; c + 32 < m6; c += 64) {   // two columns per lane in flight (distinct columns: no aliasing in colw)
+                        for (; c + 32 < m6; c += 64) {   // two columns per lane in flight (distinct columns: no aliasing in colw; four in flight measured no faster)
                             const int ca = cmap[c], cb = cmap[c + 32];
                             const double xa = sm.xJ[ca], xb = sm.xJ[cb];
                             const double wa = colw[ca], wb = colw[cb];
@@ -426,6 +476,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         }
         jdone += (unsigned int)ng;
         __syncthreads();
+        if (producer && npre > 0) prefetch(jdone);   // every chunk of this iteration is consumed: refill the ring for the next one
         if (tid == 0) {
             double v = sm.pqw[0];
 #pragma unroll
@@ -509,6 +560,10 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         t_a = now(); t_s2 += t_a - t_b;
         if (G > 1 && *reinterpret_cast<volatile int32_t*>(P.flags + FL_XCHG_TIMEOUT)) break;   // set before the barrier: uniform
     }
+    if (producer && lane < npre) {   // the prefetched copies of the iteration that did not happen must land before the CTA exits
+        const unsigned int H = (SP ? jdone : 2u * jdone) + lane;
+        ps_mbar_wait(&sm.full[H % PS_STAGES], (H / PS_STAGES) & 1u);
+    }
     if (owner) P.pcg_x[i] = x_i;
     if (b == 0 && tid == 0) {
         P.scalars[SC_RZ] = rz; P.scalars[SC_RZ_NEXT] = rz; P.scalars[SC_RZ0] = rz0;
@@ -554,7 +609,16 @@ bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStrea
     static const double l2_mb = std::getenv("SBA_PS_L2_MB") ? std::atof(std::getenv("SBA_PS_L2_MB")) : 80.0;
     int pin_hg = (int)(l2_mb * 1e6 / ((double)P.ps_grid * PS_STAGE_BYTES));
     if (P.sp_on) pin_hg = (int)(l2_mb * 1e6 / (double)P.ps_grid);   // bytes of every run
-    void* args[] = {&Pc, &tol2, &max_iters, &pin_hg};
+    // SBA_PS_MODE: bit 0 ring prefetch during the barriers / fold, bit 1 L2-resident share interleaved over the run
+    // (default: both on the block-sparse panels -- measured 57.2 -> 56.2 us per CG iteration on the Venice shape; off on the
+    // dense tiles, where neither changed the time)
+    static const int ps_mode_env = std::getenv("SBA_PS_MODE") ? std::atoi(std::getenv("SBA_PS_MODE")) : -1;
+    const int ps_mode = ps_mode_env >= 0 ? ps_mode_env : (P.sp_on ? 3 : 0);
+    double frac = P.sp_on ? l2_mb * 1e6 / std::max((double)P.sp_bytes - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0)
+                          : l2_mb * 1e6 / std::max((double)P.ex_nown * EX_TD * EX_TD * 8.0 - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0);
+    int pin_f16 = (int)(std::min(std::max(frac, 0.0), 1.0) * 65536.0);
+    int mode = ps_mode;
+    void* args[] = {&Pc, &tol2, &max_iters, &pin_hg, &pin_f16, &mode};
     return cudaLaunchCooperativeKernel(P.sp_on ? (void*)k_pcg_solve<true> : (void*)k_pcg_solve<false>, dim3(P.ps_grid), dim3(PS_THREADS), args, sizeof(PsSmem), st) == cudaSuccess;
 }
 
