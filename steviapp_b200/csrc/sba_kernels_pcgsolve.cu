@@ -221,12 +221,13 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
     uint64_t pol_keep, pol_stream;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_stream));
-    const bool do_prefetch = ps_mode & 1, do_interleave = ps_mode & 2;
+    // Block-sparse panels only: on the dense tiles neither changed the time (measured), so that variant keeps its plain loop.
+    const bool do_prefetch = SP && (ps_mode & 1), do_interleave = SP && (ps_mode & 2);
     int npre = 0;
     uint32_t pre_at = 0, pre_B = 0, pre_total = 0;
     int pre_dx = 0;
-    if (producer && do_prefetch) {
-        if constexpr (SP) {
+    if constexpr (SP) {
+        if (producer && do_prefetch) {
             const bool cand = lane < ng && lane < SP_SLOTS;
             const int4 dsc = cand ? __ldg(P.sp_chunk + q_first + lane) : make_int4(0, 0, 0, 0);
             uint32_t incl = (uint32_t)dsc.y;
@@ -235,27 +236,21 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
             npre = __popc(__ballot_sync(FULL, cand && incl <= SP_RING_BYTES));   // a prefix of the lanes: the sums grow
             pre_B = (uint32_t)dsc.y; pre_at = incl - pre_B; pre_dx = dsc.x;
             pre_total = npre > 0 ? __shfl_sync(FULL, incl, npre - 1) : 0u;
-        } else {
-            npre = min(PS_STAGES, 2 * ng);
         }
     }
     auto prefetch = [&](unsigned int jbase) {   // producer warp, ring empty
-        if (lane < npre) {
-            if constexpr (SP) {
+        if constexpr (SP) {
+            if (lane < npre) {
                 const unsigned int H = jbase + lane, slot = H % SP_SLOTS;
                 *reinterpret_cast<volatile unsigned int*>(&sm.poff[slot]) = pre_at;
                 ps_mbar_expect_tx(&sm.full[slot], pre_B);
                 ps_bulk_load_hint(reinterpret_cast<unsigned char*>(ring_flat) + pre_at,
                                   reinterpret_cast<const unsigned char*>(P.sp_data) + 16 * (size_t)(unsigned int)pre_dx, pre_B, &sm.full[slot], pol_stream);
-            } else {
-                const unsigned int H = 2u * jbase + lane, s = H % PS_STAGES;
-                ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
-                ps_bulk_load_hint(sm.ring[s], run + (size_t)lane * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s], pol_stream);
             }
+            __syncwarp();
         }
-        __syncwarp();
     };
-    if (producer && npre > 0) prefetch(0u);
+    if constexpr (SP) { if (producer && npre > 0) prefetch(0u); }
     // phase clock of CTA 0 (ns, summed over the iterations): mat-vec, barrier 1, fold + vector part, barrier 2 + scalars
     auto now = [&]() -> long long { long long t = 0; if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; };
     long long t_m = 0, t_s1 = 0, t_f = 0, t_s2 = 0, t_a = now();
@@ -326,17 +321,13 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
                 // the first pin_hg half groups of every run are loaded evict_last: S does not change during the solve, so that
                 // share of the tiles (sized to the L2 by the host) is served from L2 from the second CG iteration on; the rest
                 // streams through evict_first and cannot push it out
-                // (ring prefetch: the first npre stages are already in flight; interleave: every stage whose number crosses a
-                // multiple of 65536 / pin_f16 is kept instead of the leading pin_hg ones)
                 if constexpr (SP) { } else
-                for (unsigned int h = (unsigned int)npre; h < 2u * ng; h++) {
+                for (unsigned int h = 0; h < 2u * ng; h++) {
                     const unsigned int H = 2u * jdone + h, s = H % PS_STAGES, use = H / PS_STAGES;
                     if (use > 0) ps_mbar_wait(&sm.empty[s], (use - 1) & 1u);   // the owner warp has released the previous contents
                     ps_mbar_expect_tx(&sm.full[s], PS_STAGE_BYTES);
-                    const unsigned int hh = h - (unsigned int)npre;
-                    const bool keep = do_interleave ? (((unsigned long long)(hh + 1) * (unsigned int)pin_f16) >> 16) != (((unsigned long long)hh * (unsigned int)pin_f16) >> 16)
-                                                    : (int)h < pin_hg;
-                    ps_bulk_load_hint(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s], keep ? pol_keep : pol_stream);
+                    ps_bulk_load_hint(sm.ring[s], run + (size_t)h * PS_HALF_ROWS * EX_TD, PS_STAGE_BYTES, &sm.full[s],
+                                      (int)h < pin_hg ? pol_keep : pol_stream);
                 }
             }
         } else {
@@ -476,7 +467,7 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         }
         jdone += (unsigned int)ng;
         __syncthreads();
-        if (producer && npre > 0) prefetch(jdone);   // every chunk of this iteration is consumed: refill the ring for the next one
+        if constexpr (SP) { if (producer && npre > 0) prefetch(jdone); }   // every chunk of this iteration is consumed: refill the ring for the next one
         if (tid == 0) {
             double v = sm.pqw[0];
 #pragma unroll
@@ -560,9 +551,11 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
         t_a = now(); t_s2 += t_a - t_b;
         if (G > 1 && *reinterpret_cast<volatile int32_t*>(P.flags + FL_XCHG_TIMEOUT)) break;   // set before the barrier: uniform
     }
-    if (producer && lane < npre) {   // the prefetched copies of the iteration that did not happen must land before the CTA exits
-        const unsigned int H = (SP ? jdone : 2u * jdone) + lane;
-        ps_mbar_wait(&sm.full[H % PS_STAGES], (H / PS_STAGES) & 1u);
+    if constexpr (SP) {
+        if (producer && lane < npre) {   // the prefetched copies of the iteration that did not happen must land before the CTA exits
+            const unsigned int H = jdone + lane;
+            ps_mbar_wait(&sm.full[H % SP_SLOTS], (H / SP_SLOTS) & 1u);
+        }
     }
     if (owner) P.pcg_x[i] = x_i;
     if (b == 0 && tid == 0) {
