@@ -14,6 +14,7 @@ for f in sba_kernels sba_kernels_schur sba_kernels_op sba_kernels_mv sba_kernels
 done
 $NVCC $FLAGS -x cu -c sba_comm.cpp -o ../build/sba_comm.o & pids+=($!)
 $NVCC $FLAGS -x cu -c sba_capi.cpp -o ../build/sba_capi.o & pids+=($!)
+$NVCC $FLAGS -x cu -c sba_bal.cpp -o ../build/sba_bal.o & pids+=($!)
 for p in "${pids[@]}"; do wait $p; done
 $NVCC -shared -o $OUT ../build/*.o -ccbin $CXX_HOST -lcudart_static -ldl -lpthread -lrt
 echo "built $(readlink -f $OUT)"

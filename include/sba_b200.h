@@ -252,7 +252,7 @@ int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own,
 
 /* block-sparse copy of the tiles (one GPU, persistent PCG kernel): the CG iterations stream, per tile and block row, only the
  * 6x6 blocks that can be non-zero (two cameras that share a point) as PANELS of 6 rows with a 16-bit column map; consecutive
- * panels of a tile travel in CHUNKS of <= 19 KB (one bulk copy each).  enabled = 1 when that copy is what k_pcg_solve reads
+ * panels of a tile travel in CHUNKS of <= 40 KB (a panel directory + the panels, one bulk copy each).  enabled = 1 when that copy is what k_pcg_solve reads
  * (default: one GPU, tiles >= 64 MB and panels <= 85 % of them; SBA_PS_SPARSE=0/1 forces, also on several GPUs); n_blocks = blocks kept; stream_bytes =
  * bytes one CG iteration reads.  Same role as the block structure of Ceres' BlockRandomAccessSparseMatrix behind
  * modularsbasolver.cpp:938.  Measurement only. */
@@ -264,6 +264,29 @@ int sba_explicit_sparse_info(const sba_solver* s, int32_t* enabled, int32_t* n_p
  * block diagonal and zeros below) and the reduced right-hand side (6 * n_cams).  Any pointer may be NULL.  The analogue
  * in the reference is reading Ceres' reduced system, which Ceres does not expose; used by tests and scripts only. */
 int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* tile_j, double* rhs);
+
+/* ---- BAL text problems.  Format and camera model of the reference's in-tree BAL example
+ * (modules/g2o/g2o/examples/bal/bal_example.cpp:271-340 reads the file, :168-204 is the projection): header
+ * "cameras points observations", one "camera point x y" line per observation, 9 doubles per camera (Rodrigues r, t, f, k1,
+ * k2; world -> camera, looking down -z), 3 per point.  Host code only: these calls need no CUDA device.
+ * Errors: SBA_ERR_INVALID with the text in sba_bal_error() (unreadable file, bad header, index out of bounds -- the
+ * reference asserts the same bounds at :312-316 --, truncated file). */
+typedef struct sba_bal sba_bal;
+int sba_bal_open(const char* path, sba_bal** out);
+void sba_bal_close(sba_bal* b);
+const char* sba_bal_error(void);
+int sba_bal_sizes(const sba_bal* b, int32_t* n_cams, int32_t* n_pts, int32_t* n_obs);
+/* the file's own arrays, unconverted (any pointer may be NULL): cam_idx / pt_idx [n_obs], xy [2 n_obs], cam9 [9 n_cams], xyz [3 n_pts] */
+int sba_bal_raw(const sba_bal* b, int32_t* cam_idx, int32_t* pt_idx, double* xy, double* cam9, double* xyz);
+/* the problem in the conventions of this header, ready for sba_set_intrinsics (n_cams models {f, 0...}) / sba_set_poses /
+ * sba_set_points / sba_add_observations: sensor -> world poses looking down +z (R_e = R^T diag(1,-1,-1), t_e = -R^T t),
+ * pixels with the file's radial distortion removed and v negated (f, k1, k2 constant: FixedParameter::CameraInternal).
+ * n_undistort_failed (may be NULL) counts observations whose radius equation did not converge (kept distorted). */
+int sba_bal_convert(const sba_bal* b, double* raxis, double* t, double* intr10, int32_t* cam_model, double* xyz,
+                    int32_t* cam_idx, int32_t* pt_idx, double* uv, int32_t* n_undistort_failed);
+/* writes a BAL file (%.17g: reading it back reproduces every double) */
+int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs, const int32_t* cam_idx, const int32_t* pt_idx,
+                  const double* xy, const double* cam9, const double* xyz);
 
 const char* sba_version(void);
 

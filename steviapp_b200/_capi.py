@@ -25,6 +25,7 @@ EXPORTS = [
     "sba_evaluate_intrinsics_jacobian", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
+    "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
 ]
 
 
@@ -110,6 +111,14 @@ def load():
     lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_sparse_info.argtypes = [vp, P(i32), P(i32), P(i32), P(C.c_int64), P(C.c_int64)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
+    lib.sba_bal_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.sba_bal_close.argtypes = [vp]
+    lib.sba_bal_close.restype = None
+    lib.sba_bal_error.restype = C.c_char_p
+    lib.sba_bal_sizes.argtypes = [vp, vp, vp, vp]
+    lib.sba_bal_raw.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.sba_bal_convert.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.sba_bal_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int:   # default restype: all status-returning functions

@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -107,3 +108,121 @@ void log_rotation(const double R[9], double r[3]) {
 }
 
 }  // namespace
+
+extern "C" {
+
+const char* sba_bal_error(void) { return g_bal_error.c_str(); }
+
+int sba_bal_open(const char* path, sba_bal** out) {
+    if (!path || !out) return bal_fail("sba_bal_open: null argument");
+    *out = nullptr;
+    std::vector<char> buf;
+    if (!slurp(path, buf)) return bal_fail(std::string("sba_bal_open: cannot read ") + path);
+    Cursor c{buf.data()};
+    const long nc = c.integer(), np = c.integer(), no = c.integer();
+    if (!c.ok || nc <= 0 || np <= 0 || no < 0 || nc > 0x7fffffffL || np > 0x7fffffffL || no > 0x7fffffffL)
+        return bal_fail("sba_bal_open: bad header (expected: cameras points observations)");
+    sba_bal* b = new (std::nothrow) sba_bal;
+    if (!b) return bal_fail("sba_bal_open: out of memory");
+    b->n_cams = (int32_t)nc; b->n_pts = (int32_t)np; b->n_obs = (int32_t)no;
+    b->cam.resize((size_t)no); b->pt.resize((size_t)no); b->xy.resize(2 * (size_t)no);
+    b->cam9.resize(9 * (size_t)nc); b->xyz.resize(3 * (size_t)np);
+    for (long i = 0; i < no && c.ok; i++) {
+        const long ci = c.integer(), pi = c.integer();
+        b->xy[2 * (size_t)i] = c.real(); b->xy[2 * (size_t)i + 1] = c.real();
+        if (c.ok && (ci < 0 || ci >= nc || pi < 0 || pi >= np)) {   // the reference asserts the same bounds (bal_example.cpp:312-316)
+            delete b;
+            return bal_fail("sba_bal_open: observation " + std::to_string(i) + " has an index out of bounds");
+        }
+        b->cam[(size_t)i] = (int32_t)ci; b->pt[(size_t)i] = (int32_t)pi;
+    }
+    for (size_t k = 0; k < b->cam9.size() && c.ok; k++) b->cam9[k] = c.real();
+    for (size_t k = 0; k < b->xyz.size() && c.ok; k++) b->xyz[k] = c.real();
+    if (!c.ok) { delete b; return bal_fail("sba_bal_open: file ends early or holds a token that is not a number"); }
+    *out = b;
+    return SBA_OK;
+}
+
+void sba_bal_close(sba_bal* b) { delete b; }
+
+int sba_bal_sizes(const sba_bal* b, int32_t* n_cams, int32_t* n_pts, int32_t* n_obs) {
+    if (!b) return bal_fail("sba_bal_sizes: null handle");
+    if (n_cams) *n_cams = b->n_cams;
+    if (n_pts) *n_pts = b->n_pts;
+    if (n_obs) *n_obs = b->n_obs;
+    return SBA_OK;
+}
+
+int sba_bal_raw(const sba_bal* b, int32_t* cam_idx, int32_t* pt_idx, double* xy, double* cam9, double* xyz) {
+    if (!b) return bal_fail("sba_bal_raw: null handle");
+    if (cam_idx) std::memcpy(cam_idx, b->cam.data(), b->cam.size() * sizeof(int32_t));
+    if (pt_idx) std::memcpy(pt_idx, b->pt.data(), b->pt.size() * sizeof(int32_t));
+    if (xy) std::memcpy(xy, b->xy.data(), b->xy.size() * sizeof(double));
+    if (cam9) std::memcpy(cam9, b->cam9.data(), b->cam9.size() * sizeof(double));
+    if (xyz) std::memcpy(xyz, b->xyz.data(), b->xyz.size() * sizeof(double));
+    return SBA_OK;
+}
+
+int sba_bal_convert(const sba_bal* b, double* raxis, double* t, double* intr10, int32_t* cam_model, double* xyz,
+                    int32_t* cam_idx, int32_t* pt_idx, double* uv, int32_t* n_undistort_failed) {
+    if (!b || !raxis || !t || !intr10 || !cam_model || !xyz || !cam_idx || !pt_idx || !uv) return bal_fail("sba_bal_convert: null argument");
+    for (int32_t i = 0; i < b->n_cams; i++) {
+        const double* c9 = &b->cam9[9 * (size_t)i];
+        double R[9], Re[9];
+        rodrigues(c9, R);
+        // R_e = R^T F, F = diag(1, -1, -1): column j of R^T scaled by F_jj
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) Re[3 * r + c] = R[3 * c + r] * (c == 0 ? 1.0 : -1.0);
+        log_rotation(Re, raxis + 3 * (size_t)i);
+        for (int r = 0; r < 3; r++) t[3 * (size_t)i + r] = -(R[r] * c9[3] + R[3 + r] * c9[4] + R[6 + r] * c9[5]);   // -R^T t
+        double* m = intr10 + (size_t)SBA_INTR_STRIDE * i;
+        for (int k = 0; k < SBA_INTR_STRIDE; k++) m[k] = 0.0;
+        m[0] = c9[6];
+        cam_model[i] = i;
+    }
+    std::memcpy(xyz, b->xyz.data(), b->xyz.size() * sizeof(double));
+    int32_t failed = 0;
+    for (int32_t i = 0; i < b->n_obs; i++) {
+        const double* c9 = &b->cam9[9 * (size_t)b->cam[(size_t)i]];
+        const double f = c9[6], k1 = c9[7], k2 = c9[8];
+        const double xd = b->xy[2 * (size_t)i] / f, yd = b->xy[2 * (size_t)i + 1] / f;   // distorted normalised coordinates
+        const double rd = std::sqrt(xd * xd + yd * yd);
+        // radius before distortion: rho (1 + k1 rho^2 + k2 rho^4) = rd, Newton from rho = rd
+        double rho = rd;
+        bool ok = true;
+        for (int it = 0; it < 50; it++) {
+            const double r2 = rho * rho, g = rho * (1.0 + r2 * (k1 + k2 * r2)) - rd, dg = 1.0 + r2 * (3.0 * k1 + 5.0 * k2 * r2);
+            if (!(std::fabs(dg) > 1e-12)) { ok = false; break; }
+            const double step = g / dg;
+            rho -= step;
+            if (std::fabs(step) <= 1e-15 * std::fmax(rho, 1.0)) break;
+        }
+        // accepted when the radius equation holds (a wide-angle observation beyond the turning point of the polynomial has no
+        // root near rd: kept distorted and counted)
+        if (ok) { const double r2 = rho * rho; ok = std::fabs(rho * (1.0 + r2 * (k1 + k2 * r2)) - rd) <= 1e-12 * std::fmax(rd, 1.0); }
+        if (!ok || !(rho >= 0.0) || !std::isfinite(rho)) { rho = rd; failed++; }
+        const double s = rd > 0.0 ? rho / rd : 1.0;
+        uv[2 * (size_t)i] = f * xd * s;
+        uv[2 * (size_t)i + 1] = -f * yd * s;
+        cam_idx[i] = b->cam[(size_t)i]; pt_idx[i] = b->pt[(size_t)i];
+    }
+    if (n_undistort_failed) *n_undistort_failed = failed;
+    return SBA_OK;
+}
+
+int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs, const int32_t* cam_idx, const int32_t* pt_idx,
+                  const double* xy, const double* cam9, const double* xyz) {
+    if (!path || !cam_idx || !pt_idx || !xy || !cam9 || !xyz || n_cams <= 0 || n_pts <= 0 || n_obs < 0) return bal_fail("sba_bal_write: bad argument");
+    FILE* f = std::fopen(path, "w");
+    if (!f) return bal_fail(std::string("sba_bal_write: cannot open ") + path);
+    std::fprintf(f, "%d %d %d\n", n_cams, n_pts, n_obs);
+    for (int32_t i = 0; i < n_obs; i++)
+        std::fprintf(f, "%d %d %.17g %.17g\n", cam_idx[i], pt_idx[i], xy[2 * (size_t)i], xy[2 * (size_t)i + 1]);
+    for (size_t k = 0; k < 9 * (size_t)n_cams; k++) std::fprintf(f, "%.17g\n", cam9[k]);
+    for (size_t k = 0; k < 3 * (size_t)n_pts; k++) std::fprintf(f, "%.17g\n", xyz[k]);
+    const bool bad = std::ferror(f) != 0;
+    if (std::fclose(f) != 0 || bad) return bal_fail(std::string("sba_bal_write: write failed on ") + path);
+    return SBA_OK;
+}
+
+}  // extern "C"
