@@ -26,7 +26,7 @@ METRIC = "lm_iterations_per_s"
 UNIT = "LM iters/s"
 FIXED = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
 LM_CHUNK = 6             # LM iterations per uninterrupted solve of the timed region (restart from the initial values in between)
-SAMPLE_DIV = 16          # CPU legs run on a Venice-shape scene with 1/16 of the points (same cameras, same views/point)
+SAMPLE_DIV = 4            # CPU legs run on a Venice-shape scene with 1/4 of the points (same cameras, same views/point): ~10-20 s of CPU work
 
 
 def parse():
@@ -150,14 +150,14 @@ def bench_config(a, explicit=True):
     return {"workload": f"synthetic {a.shape}-shape BA: {nc} cameras / {npt} points / {no} observations, plane cost, "
                         "intrinsics constant, first camera fixed, 4 GCP priors",
             "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
-            "linear_solver": ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration); "
+            "linear_solver": ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; on one GPU the PCG streams them as block-sparse panels: only the 6x6 blocks of camera pairs that share a point); "
                               "whole PCG solve = one persistent cooperative kernel (TMA bulk-copy ring); multi-GPU: partial tiles reduce-scattered, "
                               "every rank applies its slice, the 6*Nc partial is all-reduced inside that kernel over NVLink peer mailboxes") if explicit else
                              ("Schur complement + SCHUR_JACOBI PCG; implicit operator (two passes over the observations per CG iteration: the explicit "
                               "tiles would be a larger stream than the observations); multi-GPU: the 6*Nc partial is all-reduced inside the fused PCG "
                               "kernel over NVLink peer mailboxes"),
             "step": "one LM iteration, fixed count (tolerances 0); solves of at most 6 LM iterations, each restarting from the same initial values",
-            "l2": ("inputs larger than L2, no flush: ~1.2 GB of observation planes per linearisation and 479 MB of tiles per CG iteration vs 126 MB L2; "
+            "l2": ("inputs larger than L2, no flush: ~1.2 GB of observation planes per linearisation and 479 MB of tiles (330 MB as block-sparse panels) per CG iteration vs 126 MB L2; "
                    "inside a PCG solve 80 MB of the tiles are deliberately kept L2-resident (evict_last) across its CG iterations"),
             "parallelism": f"points sharded over {a.gpus} GPU(s), cameras replicated"}
 

@@ -1,7 +1,7 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, bench line, ncu launch list + full capture of the dominant kernel, schedule sweep.
+# One gpurun call: GPU parity tests, bench line, ncu launch lists (profiling target and bench.py) + full capture of the dominant kernel.
 # Usage (from the repo root on the GPU box): bash scripts/round_gpu.sh <tag>
-tag=${1:-r1h}
+tag=${1:-r1i}
 mkdir -p gpurun_out
 timeout 420 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${tag}_pytest_gpu.log
 timeout 300 python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
@@ -12,5 +12,7 @@ timeout 120 python scripts/prof_target.py venice > gpurun_out/${tag}_prof_plain.
       python scripts/prof_target.py venice > gpurun_out/${tag}_ncu_full.log 2>&1
 }
 timeout 60 env SBA_PS_CLOCK=1 python scripts/prof_target.py venice > gpurun_out/${tag}_ps_clock.log 2>&1
-timeout 200 python scripts/sp_cost_sweep.py venice > gpurun_out/${tag}_sp_sweep.log 2>&1
-tail -3 gpurun_out/${tag}_pytest_gpu.log; cat gpurun_out/${tag}_bench.json | cut -c1-600; cat gpurun_out/${tag}_sp_sweep.log
+# launch list of bench.py itself (the judged command), short form; its printed numbers are not bench values
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_bench_launches.csv \
+    python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${tag}_bench_ncu.log 2>&1
+tail -3 gpurun_out/${tag}_pytest_gpu.log; cat gpurun_out/${tag}_bench.json | cut -c1-600
