@@ -150,7 +150,7 @@ def bench_config(a, explicit=True):
     return {"workload": f"synthetic {a.shape}-shape BA: {nc} cameras / {npt} points / {no} observations, plane cost, "
                         "intrinsics constant, first camera fixed, 4 GCP priors",
             "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
-            "linear_solver": ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; on one GPU the PCG streams them as block-sparse panels: only the 6x6 blocks of camera pairs that share a point); "
+            "linear_solver": ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; when a rank holds >= 64 MB of them the PCG streams them as block-sparse panels: only the 6x6 blocks of camera pairs that share a point); "
                               "whole PCG solve = one persistent cooperative kernel (TMA bulk-copy ring); multi-GPU: partial tiles reduce-scattered, "
                               "every rank applies its slice, the 6*Nc partial is all-reduced inside that kernel over NVLink peer mailboxes") if explicit else
                              ("Schur complement + SCHUR_JACOBI PCG; implicit operator (two passes over the observations per CG iteration: the explicit "

@@ -250,7 +250,7 @@ int sba_explicit_info(const sba_solver* s, int32_t* enabled, int32_t* n_tiles,
 int sba_explicit_shard(const sba_solver* s, int32_t* first_tile, int32_t* n_own, int32_t* peer_exchange,
                        int32_t* persistent_pcg);
 
-/* block-sparse copy of the tiles (one GPU, persistent PCG kernel): the CG iterations stream, per tile and block row, only the
+/* block-sparse copy of the tiles (persistent PCG kernel): the CG iterations stream, per tile and block row, only the
  * 6x6 blocks that can be non-zero (two cameras that share a point) as PANELS of 6 rows with a 16-bit column map; consecutive
  * panels of a tile travel in CHUNKS of <= 40 KB (a panel directory + the panels, one bulk copy each).  enabled = 1 when that copy is what k_pcg_solve reads
  * (default: a rank's tiles >= 64 MB and panels <= 85 % of them; SBA_PS_SPARSE=0/1 forces); n_blocks = blocks kept; stream_bytes =
