@@ -26,7 +26,7 @@ METRIC = "lm_iterations_per_s"
 UNIT = "LM iters/s"
 FIXED = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
 LM_CHUNK = 6             # LM iterations per uninterrupted solve of the timed region (restart from the initial values in between)
-SAMPLE_DIV = 4            # CPU legs run on a Venice-shape scene with 1/4 of the points (same cameras, same views/point): ~10-20 s of CPU work
+SAMPLE_DIV = 2            # CPU legs run on a Venice-shape scene with 1/2 of the points (same cameras, same views/point): ~10-15 s of CPU work on the 16-core GPU box
 
 
 def parse():
