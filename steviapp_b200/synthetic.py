@@ -235,7 +235,8 @@ def shard_scene(scene, rank, nranks, begin=None):
     out = dict(scene)
     out["n_pts"] = hi - lo
     out["pts"] = np.ascontiguousarray(scene["pts"][lo:hi])
-    out["pts_true"] = scene["pts_true"][lo:hi]
+    if "pts_true" in scene:   # synthetic scenes only (a loaded BAL file has no ground truth)
+        out["pts_true"] = scene["pts_true"][lo:hi]
     out["pt_fixed"] = np.ascontiguousarray(scene["pt_fixed"][lo:hi])
     out["obs_cam"] = np.ascontiguousarray(scene["obs_cam"][sel])
     out["obs_pt"] = np.ascontiguousarray(scene["obs_pt"][sel] - lo)

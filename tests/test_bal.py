@@ -107,6 +107,23 @@ def test_oracle_cost_is_zero_on_an_exact_bal_problem(tmp_path):
     assert ev["cost"] < 1e-16 * ci.shape[0] * 1e6, ev["cost"]
 
 
+def test_loaded_problem_shards_by_points(tmp_path):
+    """SURVEY 8(e) sharding applies to a loaded file as to the synthetic scenes: contiguous point ranges, every observation
+    on exactly one rank, cameras replicated."""
+    ci, pi, xy, cam9, xyz = make_bal(seed=2, n_cams=8, n_pts=300)
+    path = tmp_path / "problem.txt"
+    bal.write_bal(path, ci, pi, xy, cam9, xyz)
+    sc = bal.load_bal(path)
+    parts = [synthetic.shard_scene(sc, r, 3) for r in range(3)]
+    assert sum(q["n_pts"] for q in parts) == sc["n_pts"] and sum(q["n_obs"] for q in parts) == sc["n_obs"]
+    for q in parts:
+        lo, hi = q["point_range"]
+        assert np.array_equal(q["pts"], sc["pts"][lo:hi]) and np.array_equal(q["raxis"], sc["raxis"])
+        assert q["obs_pt"].min() >= 0 and q["obs_pt"].max() < q["n_pts"]
+    obs = max(q["n_obs"] for q in parts)
+    assert obs <= 1.2 * sc["n_obs"] / 3 + 10          # balanced by observation count
+
+
 @pytest.mark.parametrize("text, what", [
     ("", "bad header"), ("0 5 5\n", "bad header"), ("2 2\n", "bad header"),
     ("1 1 1\n0 3 1.0 2.0\n" + "0 " * 12, "out of bounds"), ("1 1 1\n-1 0 1.0 2.0\n" + "0 " * 12, "out of bounds"),
