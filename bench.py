@@ -351,6 +351,9 @@ def run_b200(a):
                 "frac": kern[dom]["GBps"] / peak, "traffic": traffic, "peak_source": peak_kind,
                 "alg_bytes_per_launch": kern[dom]["alg_bytes_per_launch"], "obs_per_launch": n_obs_local,
                 "share_of_step": share[dom] / (ms_total / a.steps),
+                # context only (frac stays against MEASURED_PEAKS.json): a bulk-copy ring without math streams 330 MB per pass at this
+                # rate on a B200 (scripts/bulk_ring_bench.cu, profiles/r1i_bulk_ring_bench.log); the copy peak above is read + write
+                "read_only_stream_GBps": 7429.0,
                 "kernels": {k: dict(v, frac=v["GBps"] / peak) for k, v in kern.items()}}
 
     cpu = None
