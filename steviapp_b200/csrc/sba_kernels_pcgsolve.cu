@@ -603,12 +603,11 @@ bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStrea
     int pin_hg = (int)(l2_mb * 1e6 / ((double)P.ps_grid * PS_STAGE_BYTES));
     if (P.sp_on) pin_hg = (int)(l2_mb * 1e6 / (double)P.ps_grid);   // bytes of every run
     // SBA_PS_MODE: bit 0 ring prefetch during the barriers / fold, bit 1 L2-resident share interleaved over the run
-    // (default: both on the block-sparse panels -- measured 57.2 -> 56.2 us per CG iteration on the Venice shape; off on the
-    // dense tiles, where neither changed the time)
+    // (block-sparse panels only, default both on: measured 57.2 -> 56.2 us per CG iteration on the Venice shape; the dense-tile
+    // variant ignores it -- neither changed its time).  pin_f16 / 65536 = share of the bytes behind the prefetched ones to keep.
     static const int ps_mode_env = std::getenv("SBA_PS_MODE") ? std::atoi(std::getenv("SBA_PS_MODE")) : -1;
-    const int ps_mode = ps_mode_env >= 0 ? ps_mode_env : (P.sp_on ? 3 : 0);
-    double frac = P.sp_on ? l2_mb * 1e6 / std::max((double)P.sp_bytes - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0)
-                          : l2_mb * 1e6 / std::max((double)P.ex_nown * EX_TD * EX_TD * 8.0 - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0);
+    const int ps_mode = ps_mode_env >= 0 ? ps_mode_env : 3;
+    const double frac = P.sp_on ? l2_mb * 1e6 / std::max((double)P.sp_bytes - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0) : 0.0;
     int pin_f16 = (int)(std::min(std::max(frac, 0.0), 1.0) * 65536.0);
     int mode = ps_mode;
     void* args[] = {&Pc, &tol2, &max_iters, &pin_hg, &pin_f16, &mode};
