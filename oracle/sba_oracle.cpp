@@ -145,15 +145,10 @@ inline void dir_from_uv(const double* uv, const T* f, const T* pp, const T* ks,
 // wrapped by InvertPose<.,0>, costfunctors/posedecoratorfunctors.h:1106-1155.
 // r, t are the PARAMETER blocks (sensor->world).  Returns false when the plane
 // cost sees Pbar.z < 0 (":395-399").
+// the part of UV2ParametrizedXYZCost::operator() behind world2sensor * lm_pos (costfunctors/modularuvprojection.h:395-448)
 template <class T>
-inline bool uv_cost(const T* r, const T* t, const T* lm, const T* f, const T* pp,
-                    const T* ks, const T* ts, const T* Bs, const double* uv,
-                    const double* info, int spherical, T* residual) {
-    T ri[3], ti[3];
-    rigid_inverse(r, t, ri, ti);                 // InvertPose
-    T Pbar[3];
-    angle_axis_rotate(ri, lm, Pbar);             // world2sensor * lm_pos (":394")
-    for (int i = 0; i < 3; i++) Pbar[i] = Pbar[i] + ti[i];
+inline bool uv_cost_sensor(const T* Pbar, const T* f, const T* pp, const T* ks, const T* ts, const T* Bs,
+                           const double* uv, const double* info, int spherical, T* residual) {
     if (!spherical) {
         if (val(Pbar[2]) < 0.0) return false;
     }
@@ -187,6 +182,38 @@ inline bool uv_cost(const T* r, const T* t, const T* lm, const T* f, const T* pp
         residual[1] = e1;
     }
     return true;
+}
+
+template <class T>
+inline bool uv_cost(const T* r, const T* t, const T* lm, const T* f, const T* pp,
+                    const T* ks, const T* ts, const T* Bs, const double* uv,
+                    const double* info, int spherical, T* residual) {
+    T ri[3], ti[3];
+    rigid_inverse(r, t, ri, ti);                 // InvertPose
+    T Pbar[3];
+    angle_axis_rotate(ri, lm, Pbar);             // world2sensor * lm_pos (":394")
+    for (int i = 0; i < 3; i++) Pbar[i] = Pbar[i] + ti[i];
+    return uv_cost_sensor(Pbar, f, pp, ks, ts, Bs, uv, info, spherical, residual);
+}
+
+// PoseTransform<UVCost, SourceToInitial> (costfunctors/posedecoratorfunctors.h:628-700, built at
+// sbamodules/pinholecameraprojectormodule.cpp:23,197-214): the UV cost evaluated at transformed = pose * offset, a constant
+// sensor -> body transform (r_off, t_off).  RigidBodyTransform::operator* [external, LibStevi] composes
+// x -> R(r)(R(r_off) x + t_off) + t; the cost only ever uses the composed pose through world2sensor * lm, so the
+// restatement applies the two inverses in turn instead of forming the composed axis-angle (exp(log(R)) = R):
+// Pbar = R(-r_off) ((R(-r) lm - R(-r) t) - t_off).
+template <class T>
+inline bool uv_cost_offset(const T* r, const T* t, const double* r_off, const double* t_off, const T* lm, const T* f, const T* pp,
+                           const T* ks, const T* ts, const T* Bs, const double* uv, const double* info, int spherical, T* residual) {
+    T ri[3], ti[3];
+    rigid_inverse(r, t, ri, ti);
+    T Pb[3];
+    angle_axis_rotate(ri, lm, Pb);
+    for (int i = 0; i < 3; i++) Pb[i] = Pb[i] + ti[i] - t_off[i];
+    T ro[3] = {T(-r_off[0]), T(-r_off[1]), T(-r_off[2])};
+    T Pbar[3];
+    angle_axis_rotate(ro, Pb, Pbar);
+    return uv_cost_sensor(Pbar, f, pp, ks, ts, Bs, uv, info, spherical, residual);
 }
 
 inline int nthreads(int req) {
@@ -677,6 +704,33 @@ int oracle_evaluate_intrinsics_jac(const oracle_problem* p, double* jac) {
         for (int k = 0; k < 2; k++) for (int j = 0; j < 10; j++) jac[20 * (size_t)o + 10 * k + j] = ok ? out[k].v[j] : 0.0;
     }
     return 0;
+}
+
+// n independent samples of the PoseTransform (constant sensor offset) projection cost, SURVEY 8(f) row 3: per sample pose
+// (r, t), offset (r_off, t_off), point, pixel, optional 2x2 stiffness; one intrinsics record.  Outputs: res[2n], jac_cam[12n]
+// (rows d/dr(3) d/dt(3)), jac_pt[6n], failed[n].  Duals over the 9 free scalars, as AutoDiffCostFunction<..., 2, 3, 3, 3, ...>.
+int oracle_eval_offset(int32_t n, const double* r, const double* t, const double* r_off, const double* t_off, const double* pts,
+                       const double* intr10, const double* uv, const double* info, int spherical,
+                       double* res, double* jac_cam, double* jac_pt, uint8_t* failed) {
+    typedef Jet<9> J9;
+    int bad = 0;
+    for (int32_t o = 0; o < n; o++) {
+        J9 jr[3], jt[3], x[3], f[1], pp[2], ks[3], ts[2], Bs[2], out[2];
+        for (int i = 0; i < 3; i++) { jr[i] = J9(r[3 * o + i], i); jt[i] = J9(t[3 * o + i], 3 + i); x[i] = J9(pts[3 * o + i], 6 + i); }
+        f[0] = J9(intr10[0]); pp[0] = J9(intr10[1]); pp[1] = J9(intr10[2]);
+        ks[0] = J9(intr10[3]); ks[1] = J9(intr10[4]); ks[2] = J9(intr10[5]);
+        ts[0] = J9(intr10[6]); ts[1] = J9(intr10[7]); Bs[0] = J9(intr10[8]); Bs[1] = J9(intr10[9]);
+        const bool ok = uv_cost_offset<J9>(jr, jt, r_off + 3 * o, t_off + 3 * o, x, f, pp, ks, ts, Bs, uv + 2 * o,
+                                           info ? info + 4 * o : nullptr, spherical, out);
+        if (failed) failed[o] = ok ? 0 : 1;
+        if (!ok) bad++;
+        for (int k = 0; k < 2; k++) {
+            res[2 * o + k] = ok ? out[k].a : 0.0;
+            for (int j = 0; j < 6; j++) jac_cam[12 * (size_t)o + 6 * k + j] = ok ? out[k].v[j] : 0.0;
+            for (int j = 0; j < 3; j++) jac_pt[6 * (size_t)o + 3 * k + j] = ok ? out[k].v[6 + j] : 0.0;
+        }
+    }
+    return bad;
 }
 
 int oracle_normal_blocks(const oracle_problem* p, int num_threads, double* gc, double* gp, double* Hcc, double* Hpp) {

@@ -185,6 +185,66 @@ SBA_HD bool obs_eval(const double* cc, const double* X, const double* d, const d
     return true;
 }
 
+// One observation through a CONSTANT sensor offset (PoseTransform<UVCost, SourceToInitial>,
+// costfunctors/posedecoratorfunctors.h:628-700, built at sbamodules/pinholecameraprojectormodule.cpp:197-214): the UV cost
+// at pose * offset, i.e. Pbar = Roff^T (R^T (X - t) - toff).  cc = cache record of the BODY pose, off = Roff^T row-major [9]
+// and toff [3].  Same outputs as obs_eval.  Closed form:  A = Pi Roff^T R^T = d e / d X,  d e / d t = -A,
+// d e / d r = (Pi Roff^T) [R^T (X - t)]x Jr  -- everything downstream of the linearisation stays written in A and the body pose.
+// Math only so far: checked against the oracle's duals on the host (tests/test_hostmath.py); no kernel calls it yet.
+template <bool JAC>
+SBA_HD bool obs_eval_offset(const double* cc, const double* off, const double* X, const double* d, const double* W,
+                            int spherical, double* res, double* Jc, double* Jp) {
+    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
+    const double Bx = cc[0] * vx + cc[1] * vy + cc[2] * vz;      // point in the body frame
+    const double By = cc[3] * vx + cc[4] * vy + cc[5] * vz;
+    const double Bz = cc[6] * vx + cc[7] * vy + cc[8] * vz;
+    const double ux = Bx - off[9], uy = By - off[10], uz = Bz - off[11];
+    const double Px = off[0] * ux + off[1] * uy + off[2] * uz;   // point in the sensor frame
+    const double Py = off[3] * ux + off[4] * uy + off[5] * uz;
+    const double Pz = off[6] * ux + off[7] * uy + off[8] * uz;
+    double e0, e1, p00 = 0.0, p02 = 0.0, p11 = 0.0, p12 = 0.0;
+    if (!spherical) {
+        if (Pz < 0.0) return false;
+        const double iz = 1.0 / Pz, px = Px * iz, py = Py * iz;
+        e0 = px * d[2] - d[0];
+        e1 = py * d[2] - d[1];
+        if (JAC) { const double s = d[2] * iz; p00 = s; p11 = s; p02 = -s * px; p12 = -s * py; }
+    } else {
+        const double nx2 = d[0] * d[0] + d[2] * d[2], ny2 = d[1] * d[1] + d[2] * d[2];
+        const double inx = 1.0 / sqrt(nx2), iny = 1.0 / sqrt(ny2);
+        const double cx = d[2] * inx, sx = d[0] * inx, cy = d[2] * iny, sy = d[1] * iny;
+        const double kx = nx2 / d[2], ky = ny2 / d[2];
+        e0 = atan2(cx * Px - sx * Pz, cx * Pz + sx * Px) * kx;
+        e1 = atan2(cy * Py - sy * Pz, cy * Pz + sy * Py) * ky;
+        if (JAC) {
+            const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
+            p00 = qx * Pz; p02 = -qx * Px; p11 = qy * Pz; p12 = -qy * Py;
+        }
+    }
+    if (W) { res[0] = W[0] * e0 + W[1] * e1; res[1] = W[2] * e0 + W[3] * e1; }
+    else { res[0] = e0; res[1] = e1; }
+    if (JAC) {
+        // Q = Pi Roff^T (2x3), rows (p00, 0, p02) and (0, p11, p12) times Roff^T
+        double Q[6], A[6], C[6];
+        for (int j = 0; j < 3; j++) { Q[j] = p00 * off[j] + p02 * off[6 + j]; Q[3 + j] = p11 * off[3 + j] + p12 * off[6 + j]; }
+        for (int k = 0; k < 2; k++) {
+            const double q0 = Q[3 * k], q1 = Q[3 * k + 1], q2 = Q[3 * k + 2];
+            for (int j = 0; j < 3; j++) A[3 * k + j] = q0 * cc[j] + q1 * cc[3 + j] + q2 * cc[6 + j];     // Q R^T
+            const double b0 = q1 * Bz - q2 * By, b1 = -q0 * Bz + q2 * Bx, b2 = q0 * By - q1 * Bx;        // q [B]x
+            for (int j = 0; j < 3; j++) C[3 * k + j] = b0 * cc[12 + j] + b1 * cc[15 + j] + b2 * cc[18 + j];   // ... Jr
+        }
+        for (int j = 0; j < 3; j++) {
+            const double c0 = C[j], c1 = C[3 + j], a0 = A[j], a1 = A[3 + j];
+            const double y0 = W ? W[0] * c0 + W[1] * c1 : c0, y1 = W ? W[2] * c0 + W[3] * c1 : c1;
+            const double x0 = W ? W[0] * a0 + W[1] * a1 : a0, x1 = W ? W[2] * a0 + W[3] * a1 : a1;
+            Jc[j] = y0; Jc[6 + j] = y1;
+            Jp[j] = x0; Jp[3 + j] = x1;
+            Jc[3 + j] = -x0; Jc[9 + j] = -x1;
+        }
+    }
+    return true;
+}
+
 // d res / d (f, pp[2], k[3], t[2], B[2]) of one observation, 2 x 10 row-major -- the Jacobian blocks the reference's
 // AutoDiffCostFunction<..., 2, 3,3,3, 1,2,3,2,2> produces for the five intrinsic blocks when they are free
 // (sbamodules/pinholecameraprojectormodule.cpp:105-122,302-533).  Closed form:

@@ -96,3 +96,66 @@ def test_intrinsics_jacobian_closed_form_matches_autodiff(hostmath, oracle, kw, 
     # column-wise relative error: the columns span ~8 orders of magnitude (d/dpp ~ 1, d/dk3 ~ f r^6)
     for c in range(8):
         assert relerr(j[:, :, c], jo[:, :, c]) < TOL, c
+
+
+@pytest.mark.parametrize("spherical", [0, 1])
+@pytest.mark.parametrize("with_info", [False, True])
+def test_constant_sensor_offset_matches_autodiff(hostmath, oracle, spherical, with_info):
+    """SURVEY 8(f) row 3, math half: the closed form of the PoseTransform<UVCost, SourceToInitial> cost (obs_eval_offset)
+    against the oracle's duals over the reference functor, 1e-12.  Random body poses, offsets of up to ~1 rad / 0.5 units,
+    points in front of the composed sensor pose; identity offset reproduces the plain cost."""
+    rng = np.random.default_rng(17 + spherical)
+    n = 400
+    intr = np.array([2000.0, 2000.0, 1500.0, -0.05, 0.01, 0.001, 1e-4, -1e-4, 0.0, 0.0])
+
+    def unit(k):
+        v = rng.normal(size=(k, 3))
+        return v / np.linalg.norm(v, axis=1)[:, None]
+
+    r = unit(n) * rng.uniform(0.05, 3.0, (n, 1))
+    t = rng.normal(0, 2.0, (n, 3))
+    r_off = unit(n) * rng.uniform(0.0, 1.0, (n, 1))
+    t_off = rng.normal(0, 0.5, (n, 3))
+    r_off[:20] = 0.0; t_off[:20] = 0.0                     # identity offsets
+    # sensor pose = pose * offset; points in front of it, pixels = exact projection + noise
+    Rb, Ro = synthetic.axis_angle_to_rotmat(r), synthetic.axis_angle_to_rotmat(r_off)
+    Rs = Rb @ Ro
+    ts = np.einsum("nij,nj->ni", Rb, t_off) + t
+    Ps = np.column_stack([rng.uniform(-4, 4, n), rng.uniform(-3, 3, n), rng.uniform(5, 40, n)])
+    pts = np.einsum("nij,nj->ni", Rs, Ps) + ts
+    uv = synthetic.uv_from_normalized(Ps[:, :2] / Ps[:, 2:3], intr) + rng.normal(0, 0.5, (n, 2))
+    uv = np.ascontiguousarray(uv, dtype=np.float64)
+    info = np.ascontiguousarray(rng.normal(size=(n, 2, 2)) + 2 * np.eye(2)) if with_info else None
+    off_rt = np.ascontiguousarray(np.concatenate(
+        [np.transpose(Ro, (0, 2, 1)).reshape(n, 9), t_off], axis=1))
+
+    lib = oracle.load()
+    ro = np.empty((n, 2)); jco = np.empty((n, 2, 6)); jpo = np.empty((n, 2, 3)); fo = np.zeros(n, np.uint8)
+    bad_o = lib.oracle_eval_offset(n, ptr(r), ptr(t), ptr(r_off), ptr(t_off), ptr(pts), ptr(intr), ptr(uv), ptr(info), spherical,
+                                   ptr(ro), ptr(jco), ptr(jpo), ptr(fo))
+    rh = np.empty((n, 2)); jch = np.empty((n, 2, 6)); jph = np.empty((n, 2, 3)); fh = np.zeros(n, np.uint8)
+    bad_h = hostmath.hm_eval_offset(n, ptr(r), ptr(t), ptr(off_rt), ptr(pts), ptr(intr), ptr(uv), ptr(info), spherical,
+                                    ptr(rh), ptr(jch), ptr(jph), ptr(fh))
+    assert bad_o == 0 and bad_h == 0
+    assert np.abs(ro).max() < 50.0                          # the samples are what they claim: near-exact projections
+    # Jacobians at the 1e-12 gate; the residual is a difference of ~2000-pixel quantities formed through TWO rotations on
+    # both sides (one ulp of 2000 is 4.5e-13), so its gate here is 2e-12
+    assert relerr(rh, ro) < 2 * TOL and relerr(jch, jco) < TOL and relerr(jph, jpo) < TOL
+    # identity offset = the plain cost (same closed form as obs_eval, same oracle functor as uv_cost)
+    sc = dict(obs_cam=np.arange(20, dtype=np.int32), obs_pt=np.arange(20, dtype=np.int32), raxis=r[:20].copy(), t=t[:20].copy(),
+              cost_kind=np.full(20, spherical, np.uint8), cam_model=np.zeros(20, np.int32), intrinsics=intr[None, :].copy(),
+              pts=pts[:20].copy(), obs_uv=uv[:20].copy(), obs_info=None if info is None else info[:20].copy())
+    res, jc, jp, failed, bad = hm_eval(hostmath, sc)
+    assert bad == 0 and relerr(rh[:20], res) < 1e-13 and relerr(jch[:20], jc) < 1e-13 and relerr(jph[:20], jp) < 1e-13
+
+
+def test_constant_sensor_offset_cheirality(hostmath, oracle):
+    """Plane cost: the functor fails when the point is behind the COMPOSED sensor pose (offset turned by pi about y)."""
+    intr = np.array([35.0, 320.0, 240.0, 0, 0, 0, 0, 0, 0, 0])
+    r = np.zeros((1, 3)); t = np.zeros((1, 3)); pts = np.array([[1.0, 2.0, 10.0]]); uv = np.array([[323.5, 247.0]])
+    r_off = np.array([[0.0, np.pi, 0.0]]); t_off = np.zeros((1, 3))
+    off_rt = np.ascontiguousarray(np.concatenate([synthetic.axis_angle_to_rotmat(r_off)[0].T.reshape(1, 9), t_off], axis=1))
+    out = [np.empty((1, 2)), np.empty((1, 2, 6)), np.empty((1, 2, 3)), np.zeros(1, np.uint8)]
+    assert oracle.load().oracle_eval_offset(1, ptr(r), ptr(t), ptr(r_off), ptr(t_off), ptr(pts), ptr(intr), ptr(uv), None, 0,
+                                            *[ptr(a) for a in out]) == 1
+    assert hostmath.hm_eval_offset(1, ptr(r), ptr(t), ptr(off_rt), ptr(pts), ptr(intr), ptr(uv), None, 0, *[ptr(a) for a in out]) == 1
