@@ -216,6 +216,30 @@ inline bool uv_cost_offset(const T* r, const T* t, const double* r_off, const do
     return uv_cost_sensor(Pbar, f, pp, ks, ts, Bs, uv, info, spherical, residual);
 }
 
+// PoseTransform<LeverArm<UVCost, Body2World | Sensor2Body, 0>, SourceToInitial, 0> (costfunctors/posedecoratorfunctors.h:148-264 for
+// ApplyLeverArm -- sensor2world = body2world * sensor2body at ":208", alias at ":500" --, :628-700 for PoseTransform; built at
+// sbamodules/pinholecameraprojectormodule.cpp:21,25,147-166 with the blocks pose r, pose t, boresight, lever arm, point, intrinsics):
+// the UV cost at (pose * offset) * (boresight, leverArm).  As in uv_cost_offset the inverses are applied in turn:
+// Pbar = R(-b) ( R(-r_off) (R(-r)(lm - t) - t_off) - l ).
+template <class T>
+inline bool uv_cost_leverarm(const T* r, const T* t, const T* b, const T* l, const double* r_off, const double* t_off, const T* lm,
+                             const T* f, const T* pp, const T* ks, const T* ts, const T* Bs, const double* uv, const double* info,
+                             int spherical, T* residual) {
+    T ri[3], ti[3];
+    rigid_inverse(r, t, ri, ti);
+    T Pb[3];
+    angle_axis_rotate(ri, lm, Pb);
+    for (int i = 0; i < 3; i++) Pb[i] = Pb[i] + ti[i] - t_off[i];
+    T ro[3] = {T(-r_off[0]), T(-r_off[1]), T(-r_off[2])};
+    T Pm[3];
+    angle_axis_rotate(ro, Pb, Pm);
+    for (int i = 0; i < 3; i++) Pm[i] = Pm[i] - l[i];
+    T bi[3] = {-b[0], -b[1], -b[2]};
+    T Pbar[3];
+    angle_axis_rotate(bi, Pm, Pbar);
+    return uv_cost_sensor(Pbar, f, pp, ks, ts, Bs, uv, info, spherical, residual);
+}
+
 inline int nthreads(int req) {
 #ifdef _OPENMP
     int mx = omp_get_max_threads();
@@ -704,6 +728,36 @@ int oracle_evaluate_intrinsics_jac(const oracle_problem* p, double* jac) {
         for (int k = 0; k < 2; k++) for (int j = 0; j < 10; j++) jac[20 * (size_t)o + 10 * k + j] = ok ? out[k].v[j] : 0.0;
     }
     return 0;
+}
+
+// n independent samples of the lever-arm projection cost: outputs res[2n], jac_cam[12n] (d/dr d/dt), jac_la[12n]
+// (d/d boresight, d/d leverArm), jac_pt[6n], failed[n]; duals over the 15 free scalars
+int oracle_eval_leverarm(int32_t n, const double* r, const double* t, const double* b, const double* l, const double* r_off,
+                         const double* t_off, const double* pts, const double* intr10, const double* uv, const double* info,
+                         int spherical, double* res, double* jac_cam, double* jac_la, double* jac_pt, uint8_t* failed) {
+    typedef Jet<15> J;
+    int bad = 0;
+    for (int32_t o = 0; o < n; o++) {
+        J jr[3], jt[3], jb[3], jl[3], x[3], f[1], pp[2], ks[3], ts[2], Bs[2], out[2];
+        for (int i = 0; i < 3; i++) {
+            jr[i] = J(r[3 * o + i], i); jt[i] = J(t[3 * o + i], 3 + i); jb[i] = J(b[3 * o + i], 6 + i); jl[i] = J(l[3 * o + i], 9 + i);
+            x[i] = J(pts[3 * o + i], 12 + i);
+        }
+        f[0] = J(intr10[0]); pp[0] = J(intr10[1]); pp[1] = J(intr10[2]);
+        ks[0] = J(intr10[3]); ks[1] = J(intr10[4]); ks[2] = J(intr10[5]);
+        ts[0] = J(intr10[6]); ts[1] = J(intr10[7]); Bs[0] = J(intr10[8]); Bs[1] = J(intr10[9]);
+        const bool ok = uv_cost_leverarm<J>(jr, jt, jb, jl, r_off + 3 * o, t_off + 3 * o, x, f, pp, ks, ts, Bs, uv + 2 * o,
+                                            info ? info + 4 * o : nullptr, spherical, out);
+        if (failed) failed[o] = ok ? 0 : 1;
+        if (!ok) bad++;
+        for (int k = 0; k < 2; k++) {
+            res[2 * o + k] = ok ? out[k].a : 0.0;
+            for (int j = 0; j < 6; j++) jac_cam[12 * (size_t)o + 6 * k + j] = ok ? out[k].v[j] : 0.0;
+            for (int j = 0; j < 6; j++) jac_la[12 * (size_t)o + 6 * k + j] = ok ? out[k].v[6 + j] : 0.0;
+            for (int j = 0; j < 3; j++) jac_pt[6 * (size_t)o + 3 * k + j] = ok ? out[k].v[12 + j] : 0.0;
+        }
+    }
+    return bad;
 }
 
 // n independent samples of the PoseTransform (constant sensor offset) projection cost, SURVEY 8(f) row 3: per sample pose

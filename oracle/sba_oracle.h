@@ -100,6 +100,11 @@ int oracle_evaluate(const oracle_problem* p, int num_threads, double* cost,
 
 /* Jacobian w.r.t. the five intrinsic blocks (n_obs*2*10) -- "next" row f1. */
 int oracle_evaluate_intrinsics_jac(const oracle_problem* p, double* jac_intr);
+/* PoseTransform<LeverArm<UVCost>> (free boresight + lever arm behind a constant offset; costfunctors/posedecoratorfunctors.h:148-264,500,
+ * sbamodules/pinholecameraprojectormodule.cpp:147-166), n independent samples; returns the number of failed evaluations */
+int oracle_eval_leverarm(int32_t n, const double* r, const double* t, const double* b, const double* l, const double* r_off,
+                         const double* t_off, const double* pts, const double* intr10, const double* uv, const double* info,
+                         int spherical, double* res, double* jac_cam, double* jac_la, double* jac_pt, uint8_t* failed);
 /* PoseTransform<UVCost, SourceToInitial> (constant sensor offset; costfunctors/posedecoratorfunctors.h:628-700,
  * sbamodules/pinholecameraprojectormodule.cpp:197-214), n independent samples; returns the number of failed evaluations */
 int oracle_eval_offset(int32_t n, const double* r, const double* t, const double* r_off, const double* t_off, const double* pts,

@@ -245,6 +245,75 @@ SBA_HD bool obs_eval_offset(const double* cc, const double* off, const double* X
     return true;
 }
 
+// One observation through a constant offset AND a free boresight / lever arm (SURVEY 8(f) row 3;
+// PoseTransform<LeverArm<UVCost, Body2World | Sensor2Body, 0>, SourceToInitial, 0>, costfunctors/posedecoratorfunctors.h:148-264,500,
+// built at sbamodules/pinholecameraprojectormodule.cpp:147-166): sensor2world = (pose * offset) * (boresight b, lever arm l), i.e.
+// Pbar = Rb^T (Roff^T (R^T (X - t) - toff) - l).  cc = cache record of the body pose, off = Roff^T [9] + toff [3],
+// cl = pose_cache(b, l) (Rb^T, l, Jr(b)).  Outputs as obs_eval plus Jl[12] = rows [d/db(3) d/dl(3)].  Closed form, with
+// G = Pi Rb^T:  d e / d l = -G,  d e / d b = Pi [Pbar]x Jr(b),  A = G Roff^T R^T = d e / d X = -d e / d t,
+// d e / d r = (G Roff^T) [R^T (X - t)]x Jr(r).  Math only so far (host parity test); no kernel calls it yet.
+template <bool JAC>
+SBA_HD bool obs_eval_leverarm(const double* cc, const double* off, const double* cl, const double* X, const double* d, const double* W,
+                              int spherical, double* res, double* Jc, double* Jl, double* Jp) {
+    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
+    const double Bx = cc[0] * vx + cc[1] * vy + cc[2] * vz;      // body frame
+    const double By = cc[3] * vx + cc[4] * vy + cc[5] * vz;
+    const double Bz = cc[6] * vx + cc[7] * vy + cc[8] * vz;
+    const double ux = Bx - off[9], uy = By - off[10], uz = Bz - off[11];
+    const double mx = off[0] * ux + off[1] * uy + off[2] * uz - cl[9];    // mounting frame, lever arm removed
+    const double my = off[3] * ux + off[4] * uy + off[5] * uz - cl[10];
+    const double mz = off[6] * ux + off[7] * uy + off[8] * uz - cl[11];
+    const double Px = cl[0] * mx + cl[1] * my + cl[2] * mz;      // sensor frame
+    const double Py = cl[3] * mx + cl[4] * my + cl[5] * mz;
+    const double Pz = cl[6] * mx + cl[7] * my + cl[8] * mz;
+    double e0, e1, p00 = 0.0, p02 = 0.0, p11 = 0.0, p12 = 0.0;
+    if (!spherical) {
+        if (Pz < 0.0) return false;
+        const double iz = 1.0 / Pz, px = Px * iz, py = Py * iz;
+        e0 = px * d[2] - d[0];
+        e1 = py * d[2] - d[1];
+        if (JAC) { const double s = d[2] * iz; p00 = s; p11 = s; p02 = -s * px; p12 = -s * py; }
+    } else {
+        const double nx2 = d[0] * d[0] + d[2] * d[2], ny2 = d[1] * d[1] + d[2] * d[2];
+        const double inx = 1.0 / sqrt(nx2), iny = 1.0 / sqrt(ny2);
+        const double cx = d[2] * inx, sx = d[0] * inx, cy = d[2] * iny, sy = d[1] * iny;
+        const double kx = nx2 / d[2], ky = ny2 / d[2];
+        e0 = atan2(cx * Px - sx * Pz, cx * Pz + sx * Px) * kx;
+        e1 = atan2(cy * Py - sy * Pz, cy * Pz + sy * Py) * ky;
+        if (JAC) {
+            const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
+            p00 = qx * Pz; p02 = -qx * Px; p11 = qy * Pz; p12 = -qy * Py;
+        }
+    }
+    if (W) { res[0] = W[0] * e0 + W[1] * e1; res[1] = W[2] * e0 + W[3] * e1; }
+    else { res[0] = e0; res[1] = e1; }
+    if (JAC) {
+        double G[6], Q[6], A[6], C[6], Cb[6];
+        const double pi0[3] = {p00, 0.0, p02}, pi1[3] = {0.0, p11, p12};
+        for (int k = 0; k < 2; k++) {
+            const double* pi = k ? pi1 : pi0;
+            for (int j = 0; j < 3; j++) G[3 * k + j] = pi[0] * cl[j] + pi[1] * cl[3 + j] + pi[2] * cl[6 + j];                 // Pi Rb^T
+            for (int j = 0; j < 3; j++) Q[3 * k + j] = G[3 * k] * off[j] + G[3 * k + 1] * off[3 + j] + G[3 * k + 2] * off[6 + j];   // G Roff^T
+            for (int j = 0; j < 3; j++) A[3 * k + j] = Q[3 * k] * cc[j] + Q[3 * k + 1] * cc[3 + j] + Q[3 * k + 2] * cc[6 + j];      // Q R^T
+            const double q0 = Q[3 * k], q1 = Q[3 * k + 1], q2 = Q[3 * k + 2];
+            const double b0 = q1 * Bz - q2 * By, b1 = -q0 * Bz + q2 * Bx, b2 = q0 * By - q1 * Bx;                              // q [B]x
+            for (int j = 0; j < 3; j++) C[3 * k + j] = b0 * cc[12 + j] + b1 * cc[15 + j] + b2 * cc[18 + j];                    // ... Jr(r)
+            const double s0 = pi[1] * Pz - pi[2] * Py, s1 = -pi[0] * Pz + pi[2] * Px, s2 = pi[0] * Py - pi[1] * Px;            // pi [Pbar]x
+            for (int j = 0; j < 3; j++) Cb[3 * k + j] = s0 * cl[12 + j] + s1 * cl[15 + j] + s2 * cl[18 + j];                   // ... Jr(b)
+        }
+        for (int j = 0; j < 3; j++) {
+            const double w00 = W ? W[0] : 1.0, w01 = W ? W[1] : 0.0, w10 = W ? W[2] : 0.0, w11 = W ? W[3] : 1.0;
+            const double a0 = w00 * A[j] + w01 * A[3 + j], a1 = w10 * A[j] + w11 * A[3 + j];
+            Jc[j] = w00 * C[j] + w01 * C[3 + j];      Jc[6 + j] = w10 * C[j] + w11 * C[3 + j];
+            Jc[3 + j] = -a0;                          Jc[9 + j] = -a1;
+            Jp[j] = a0;                               Jp[3 + j] = a1;
+            Jl[j] = w00 * Cb[j] + w01 * Cb[3 + j];    Jl[6 + j] = w10 * Cb[j] + w11 * Cb[3 + j];
+            Jl[3 + j] = -(w00 * G[j] + w01 * G[3 + j]); Jl[9 + j] = -(w10 * G[j] + w11 * G[3 + j]);
+        }
+    }
+    return true;
+}
+
 // d res / d (f, pp[2], k[3], t[2], B[2]) of one observation, 2 x 10 row-major -- the Jacobian blocks the reference's
 // AutoDiffCostFunction<..., 2, 3,3,3, 1,2,3,2,2> produces for the five intrinsic blocks when they are free
 // (sbamodules/pinholecameraprojectormodule.cpp:105-122,302-533).  Closed form:

@@ -159,3 +159,52 @@ def test_constant_sensor_offset_cheirality(hostmath, oracle):
     assert oracle.load().oracle_eval_offset(1, ptr(r), ptr(t), ptr(r_off), ptr(t_off), ptr(pts), ptr(intr), ptr(uv), None, 0,
                                             *[ptr(a) for a in out]) == 1
     assert hostmath.hm_eval_offset(1, ptr(r), ptr(t), ptr(off_rt), ptr(pts), ptr(intr), ptr(uv), None, 0, *[ptr(a) for a in out]) == 1
+
+
+@pytest.mark.parametrize("spherical", [0, 1])
+@pytest.mark.parametrize("with_info", [False, True])
+def test_lever_arm_behind_offset_matches_autodiff(hostmath, oracle, spherical, with_info):
+    """SURVEY 8(f) row 3, math half: PoseTransform<LeverArm<UVCost>> -- free boresight and lever arm behind a constant offset --
+    as a closed form (obs_eval_leverarm) against the oracle's duals over the 15 free scalars; with boresight = lever arm = 0
+    it reproduces the constant-offset cost."""
+    rng = np.random.default_rng(29 + spherical)
+    n = 400
+    intr = np.array([2000.0, 2000.0, 1500.0, -0.05, 0.01, 0.001, 1e-4, -1e-4, 0.0, 0.0])
+
+    def unit(k):
+        v = rng.normal(size=(k, 3))
+        return v / np.linalg.norm(v, axis=1)[:, None]
+
+    r = unit(n) * rng.uniform(0.05, 3.0, (n, 1)); t = rng.normal(0, 2.0, (n, 3))
+    r_off = unit(n) * rng.uniform(0.0, 1.0, (n, 1)); t_off = rng.normal(0, 0.5, (n, 3))
+    b = unit(n) * rng.uniform(0.0, 0.5, (n, 1)); l = rng.normal(0, 0.3, (n, 3))
+    b[:20] = 0.0; l[:20] = 0.0
+    Rb, Ro, Rl = (synthetic.axis_angle_to_rotmat(a) for a in (r, r_off, b))
+    Rs = Rb @ Ro @ Rl
+    ts = np.einsum("nij,nj->ni", Rb, np.einsum("nij,nj->ni", Ro, l) + t_off) + t
+    Ps = np.column_stack([rng.uniform(-4, 4, n), rng.uniform(-3, 3, n), rng.uniform(5, 40, n)])
+    pts = np.einsum("nij,nj->ni", Rs, Ps) + ts
+    uv = np.ascontiguousarray(synthetic.uv_from_normalized(Ps[:, :2] / Ps[:, 2:3], intr) + rng.normal(0, 0.5, (n, 2)))
+    info = np.ascontiguousarray(rng.normal(size=(n, 2, 2)) + 2 * np.eye(2)) if with_info else None
+    off_rt = np.ascontiguousarray(np.concatenate([np.transpose(Ro, (0, 2, 1)).reshape(n, 9), t_off], axis=1))
+
+    def outs():
+        return [np.empty((n, 2)), np.empty((n, 2, 6)), np.empty((n, 2, 6)), np.empty((n, 2, 3)), np.zeros(n, np.uint8)]
+
+    o = outs()
+    assert oracle.load().oracle_eval_leverarm(n, ptr(r), ptr(t), ptr(b), ptr(l), ptr(r_off), ptr(t_off), ptr(pts), ptr(intr), ptr(uv),
+                                              ptr(info), spherical, *[ptr(a) for a in o]) == 0
+    h = outs()
+    assert hostmath.hm_eval_leverarm(n, ptr(r), ptr(t), ptr(b), ptr(l), ptr(off_rt), ptr(pts), ptr(intr), ptr(uv), ptr(info), spherical,
+                                     *[ptr(a) for a in h]) == 0
+    assert np.abs(o[0]).max() < 50.0
+    # residual gate 3e-12: a difference of ~2000-pixel quantities behind THREE rotations (see the offset test); Jacobians 1e-12
+    assert relerr(h[0], o[0]) < 3 * TOL
+    assert relerr(h[1], o[1]) < TOL and relerr(h[2], o[2]) < TOL and relerr(h[3], o[3]) < TOL
+    # boresight = lever arm = 0: the constant-offset closed form
+    k = 20
+    rh = np.empty((k, 2)); jch = np.empty((k, 2, 6)); jph = np.empty((k, 2, 3)); fh = np.zeros(k, np.uint8)
+    assert hostmath.hm_eval_offset(k, ptr(r[:k].copy()), ptr(t[:k].copy()), ptr(off_rt[:k].copy()), ptr(pts[:k].copy()), ptr(intr),
+                                   ptr(uv[:k].copy()), ptr(None if info is None else info[:k].copy()), spherical,
+                                   ptr(rh), ptr(jch), ptr(jph), ptr(fh)) == 0
+    assert relerr(h[0][:k], rh) < 1e-13 and relerr(h[1][:k], jch) < 1e-13 and relerr(h[3][:k], jph) < 1e-13
