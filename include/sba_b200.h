@@ -288,6 +288,14 @@ int sba_bal_convert(const sba_bal* b, double* raxis, double* t, double* intr10, 
 int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs, const int32_t* cam_idx, const int32_t* pt_idx,
                   const double* xy, const double* cam9, const double* xyz);
 
+/* Push-broom sensors on the pinhole kernels, intrinsics held constant.  Replaces
+ * PinholePushbroomUVProjector::dirFromUV (sbamodules/pinholecameraprojectormodule.h:79-116): d = (u - pp + du(s), v + dv(s), f),
+ * s = (u - W/2)/W, du / dv = degree-5 polynomials with coefficients as6 / bs6.  Writes the pixels (d_x, d_y) that, with the
+ * intrinsics record {f, 0, ...} written to intr10_out (may be NULL), give the same view ray through the pinhole model, so
+ * the observations can go to sba_add_observations unchanged.  Host code only. */
+int sba_pushbroom_equivalent_uv(int32_t n, const double* uv, double sensor_width, double f, double pp, const double* as6,
+                                const double* bs6, double* uv_out, double* intr10_out);
+
 const char* sba_version(void);
 
 #ifdef __cplusplus

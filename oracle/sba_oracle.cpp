@@ -685,6 +685,14 @@ int oracle_uv_from_dir(const double* xn, const double* in, double* uv) {
 
 // test hooks on the LibStevi restatements, pinned by the reference's own vectors
 // (tests/test_geometry/testRotations.cpp:25-78, tests/test_functional_utils/main.cpp:198-218)
+// PinholePushbroomUVProjector::dirFromUV, sbamodules/pinholecameraprojectormodule.h:86-110 (params f[1], pp[1], as[6], bs[6])
+void oracle_pushbroom_dir(const double* uv, double sensor_width, double f, double pp, const double* as, const double* bs, double* dir3) {
+    const double s = (uv[0] - sensor_width / 2.0) / sensor_width;
+    const double s2 = s * s, s3 = s2 * s, s4 = s3 * s, s5 = s4 * s;
+    const double du = as[0] + as[1] * s + as[2] * s2 + as[3] * s3 + as[4] * s4 + as[5] * s5;
+    const double dv = bs[0] + bs[1] * s + bs[2] * s2 + bs[3] * s3 + bs[4] * s4 + bs[5] * s5;
+    dir3[0] = uv[0] - pp + du; dir3[1] = uv[1] + dv; dir3[2] = f;
+}
 void oracle_angle_axis_rotate(const double* r, const double* x, double* out) { angle_axis_rotate<double>(r, x, out); }
 void oracle_rigid_inverse(const double* r, const double* t, double* ri, double* ti) { rigid_inverse<double>(r, t, ri, ti); }
 

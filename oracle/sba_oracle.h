@@ -99,6 +99,7 @@ int oracle_evaluate(const oracle_problem* p, int num_threads, double* cost,
                     uint8_t* failed);
 
 /* Jacobian w.r.t. the five intrinsic blocks (n_obs*2*10) -- "next" row f1. */
+void oracle_pushbroom_dir(const double* uv, double sensor_width, double f, double pp, const double* as6, const double* bs6, double* dir3);
 int oracle_evaluate_intrinsics_jac(const oracle_problem* p, double* jac_intr);
 /* PoseTransform<LeverArm<UVCost>> (free boresight + lever arm behind a constant offset; costfunctors/posedecoratorfunctors.h:148-264,500,
  * sbamodules/pinholecameraprojectormodule.cpp:147-166), n independent samples; returns the number of failed evaluations */

@@ -26,6 +26,7 @@ EXPORTS = [
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
     "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
+    "sba_pushbroom_equivalent_uv",
 ]
 
 
@@ -118,6 +119,7 @@ def load():
     lib.sba_bal_sizes.argtypes = [vp, vp, vp, vp]
     lib.sba_bal_raw.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.sba_bal_convert.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.sba_pushbroom_equivalent_uv.argtypes = [C.c_int32, vp, C.c_double, C.c_double, C.c_double, vp, vp, vp, vp]
     lib.sba_bal_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
