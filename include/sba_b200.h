@@ -187,6 +187,14 @@ int sba_normal_blocks(sba_solver* s, double* gc, double* gp, double* Hcc, double
  * holds the intrinsics constant (FixedParameter::CameraInternal). */
 int sba_evaluate_intrinsics_jacobian(sba_solver* s, double* jac_intr);
 
+/* Residuals and Jacobians with a CONSTANT sensor offset per camera: the cost the reference builds as
+ * PoseTransform<UVCost, SourceToInitial> (costfunctors/posedecoratorfunctors.h:628-700,
+ * sbamodules/pinholecameraprojectormodule.cpp:197-214), i.e. the UV cost at pose * offset.  off12 = per camera Roff^T
+ * (row-major 3x3) followed by toff; outputs in caller order: residuals [2 n_obs], jac_cam [n_obs x 2 x 6] (d/drAxis, d/dt of
+ * the BODY pose), jac_pt [n_obs x 2 x 3]; n_failed (may be NULL) counts plane-cost evaluations behind the composed sensor
+ * pose (zeros written).  Inspection / parity hook: the LM itself does not take offsets yet. */
+int sba_evaluate_offset(sba_solver* s, const double* off12, double* residuals, double* jac_cam, double* jac_pt, int32_t* n_failed);
+
 /* y = S x and reduced rhs for explicit damping diagonals lam_c (6*n_cams), lam_p (3*n_pts) */
 int sba_schur_matvec(sba_solver* s, const double* lam_c, const double* lam_p,
                      const double* x, double* y, double* rhs);

@@ -22,7 +22,7 @@ EXPORTS = [
     "sba_default_options", "sba_create", "sba_destroy", "sba_last_error", "sba_create_error",
     "sba_set_intrinsics", "sba_set_poses", "sba_set_points", "sba_add_observations", "sba_add_priors",
     "sba_finalize", "sba_upload_parameters", "sba_download_parameters", "sba_evaluate",
-    "sba_evaluate_intrinsics_jacobian", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
+    "sba_evaluate_intrinsics_jacobian", "sba_evaluate_offset", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
     "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
@@ -112,6 +112,7 @@ def load():
     lib.sba_explicit_shard.argtypes = [vp, P(i32), P(i32), P(i32), P(i32)]
     lib.sba_explicit_sparse_info.argtypes = [vp, P(i32), P(i32), P(i32), P(C.c_int64), P(C.c_int64)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
+    lib.sba_evaluate_offset.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.sba_bal_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.sba_bal_close.argtypes = [vp]
     lib.sba_bal_close.restype = None

@@ -83,6 +83,9 @@ int sba_triangulate(sba_solver* s, int32_t n_points, const int32_t* view_off, co
     GUARD(s); return s->impl.triangulate(n_points, view_off, view_cam, view_uv, xyz_out, ok_out, ms_kernel);
 }
 int sba_evaluate_intrinsics_jacobian(sba_solver* s, double* jac_intr) { GUARD(s); return s->impl.evaluate_intrinsics_jacobian(jac_intr); }
+int sba_evaluate_offset(sba_solver* s, const double* off12, double* residuals, double* jac_cam, double* jac_pt, int32_t* n_failed) {
+    GUARD(s); return s->impl.evaluate_offset(off12, residuals, jac_cam, jac_pt, n_failed);
+}
 
 int sba_comm_unique_id(uint8_t id128[128]) {
     std::string err;

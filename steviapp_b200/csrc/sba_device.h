@@ -249,6 +249,8 @@ void launch_grad_max(const DevProblem& P, cudaStream_t st);
 void launch_gather_outputs(const DevProblem& P, const int32_t* slot_of_obs, double* res_out, double* jc_out,
                            double* jp_out, cudaStream_t st);
 void launch_intrinsics_jacobian(const DevProblem& P, const int32_t* slot_of_obs, double* jac_out, cudaStream_t st);   // 2 x 10 per observation
+void launch_evaluate_offset(const DevProblem& P, const int32_t* slot_of_obs, const double* off, double* res_out, double* jc_out,
+                            double* jp_out, int* n_failed, cudaStream_t st);   // constant sensor offset per camera (12 doubles)
 void launch_unpack_blocks(const DevProblem& P, double* Hcc36, double* Hpp9, double* gp3, cudaStream_t st);
 void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* lam_p3, cudaStream_t st);
 void launch_pack_points(const double* xyz3, double* pts4, int n, cudaStream_t st);

@@ -115,6 +115,41 @@ void launch_intrinsics_jacobian(const DevProblem& P, const int32_t* slot_of_obs,
     if (P.No) k_intrinsics_jacobian<<<cdiv(P.No, 128), 128, 0, st>>>(P, slot_of_obs, jac_out);
 }
 
+// constant-sensor-offset hook: residuals and Jacobians of every observation with the per-camera offset
+// off[12 cam] = Roff^T row-major + toff, caller order; failed evaluations (plane cost behind the composed sensor pose) write
+// zeros and are counted.  Thread per observation, same camera lookup as the intrinsics hook.
+__global__ void __launch_bounds__(128) k_evaluate_offset(DevProblem P, const int32_t* __restrict__ slot_of_obs, const double* __restrict__ off,
+                                                         double* res_out, double* jc_out, double* jp_out, int* n_failed) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.No) return;
+    const int s = slot_of_obs[i];
+    int lo = 0, hi = P.Nt - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(P.tile_start + mid) <= s) lo = mid; else hi = mid - 1;
+    }
+    const int cam = __ldg(P.tile_cam + lo), pt = P.obs_pt[s];
+    const size_t Ns = (size_t)P.Ns;
+    double W[4], d[3], r[2] = {0.0, 0.0}, Jc[12], Jp[6];
+    if (P.obs_info) for (int k = 0; k < 4; k++) W[k] = P.obs_info[(size_t)k * Ns + s];
+    dir_from_uv(P.obs_uv[2 * (size_t)s], P.obs_uv[2 * (size_t)s + 1], P.intr + 10 * P.cam_model[cam], d);
+    const bool ok = obs_eval_offset<true>(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam, off + 12 * (size_t)cam, P.pts + 4 * (size_t)pt, d,
+                                          P.obs_info ? W : nullptr, P.cam_kind[cam], r, Jc, Jp);
+    if (!ok) {
+        atomicAdd(n_failed, 1);
+        r[0] = r[1] = 0.0;
+        for (int k = 0; k < 12; k++) Jc[k] = 0.0;
+        for (int k = 0; k < 6; k++) Jp[k] = 0.0;
+    }
+    res_out[2 * (size_t)i] = r[0]; res_out[2 * (size_t)i + 1] = r[1];
+    for (int k = 0; k < 12; k++) jc_out[12 * (size_t)i + k] = Jc[k];
+    for (int k = 0; k < 6; k++) jp_out[6 * (size_t)i + k] = Jp[k];
+}
+void launch_evaluate_offset(const DevProblem& P, const int32_t* slot_of_obs, const double* off, double* res_out, double* jc_out,
+                            double* jp_out, int* n_failed, cudaStream_t st) {
+    if (P.No) k_evaluate_offset<<<cdiv(P.No, 128), 128, 0, st>>>(P, slot_of_obs, off, res_out, jc_out, jp_out, n_failed);
+}
+
 __global__ void k_pack_points(const double* __restrict__ xyz3, double* pts4, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;

@@ -80,6 +80,7 @@ public:
     int download_parameters();
     int evaluate(double* cost, double* residuals, double* jac_cam, double* jac_pt);
     int evaluate_intrinsics_jacobian(double* jac20);
+    int evaluate_offset(const double* off12, double* res, double* jac_cam, double* jac_pt, int32_t* n_failed);
     int normal_blocks(double* gc, double* gp, double* Hcc, double* Hpp);
     int schur_matvec(const double* lam_c, const double* lam_p, const double* x, double* y, double* rhs);
     int solve(int copy_params, sba_summary* sum);

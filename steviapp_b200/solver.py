@@ -193,6 +193,17 @@ class SBASolver:
         self._check(self._lib.sba_evaluate_intrinsics_jacobian(self._h, _ptr(j)))
         return j
 
+    def evaluate_offset(self, off12):
+        """Residuals / Jacobians with a constant sensor offset per camera (off12: (n_cams, 12) = Roff^T row-major + toff);
+        returns dict(residuals (n_obs, 2), jac_cam (n_obs, 2, 6), jac_pt (n_obs, 2, 3), n_failed), caller order."""
+        self.finalize()
+        n = self.sizes()["n_obs"]
+        off12 = np.ascontiguousarray(off12, dtype=np.float64)
+        assert off12.shape == (self.sizes()["n_cams"], 12)
+        r = np.empty((n, 2)); jc = np.empty((n, 2, 6)); jp = np.empty((n, 2, 3)); nf = C.c_int32()
+        self._check(self._lib.sba_evaluate_offset(self._h, _ptr(off12), _ptr(r), _ptr(jc), _ptr(jp), C.byref(nf)))
+        return {"residuals": r, "jac_cam": jc, "jac_pt": jp, "n_failed": nf.value}
+
     def explicit_info(self):
         """Static sizes of the explicit reduced camera system (enabled = the PCG applies S from the tiles)."""
         v = [C.c_int32() for _ in range(4)]
