@@ -6,7 +6,7 @@ Venice-shape bundle adjustment (1778 cameras / 993 923 points / 5 001 946 observ
   python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path (oracle port), host cores
 
 A "step" is ONE Levenberg-Marquardt iteration: damping + point-block inversion + reduced rhs +
-SCHUR_JACOBI preconditioner + PCG on the implicit Schur complement + back-substitution + trial cost
+SCHUR_JACOBI preconditioner + explicit reduced camera system + PCG (one persistent kernel) + back-substitution + trial cost
 (+ re-linearisation when the step is accepted).  Prints ONE JSON line (rank 0).
 """
 import argparse
@@ -26,7 +26,6 @@ METRIC = "lm_iterations_per_s"
 UNIT = "LM iters/s"
 FIXED = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
 LM_CHUNK = 6             # LM iterations per uninterrupted solve of the timed region (restart from the initial values in between)
-SAMPLE_DIV = 2            # CPU legs run on a Venice-shape scene with 1/2 of the points (same cameras, same views/point): ~10-15 s of CPU work on the 16-core GPU box
 
 
 def parse():
@@ -40,6 +39,7 @@ def parse():
     ap.add_argument("--pcg-max-iters", type=int, default=500)
     ap.add_argument("--pcg-check-every", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-single-thread", action="store_true", help="reference arm: skip the 1-thread LM iteration (the reference's real configuration)")
     return ap.parse_args()
 
 
@@ -90,55 +90,87 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU legs (oracle)
-def sample_scene(shape):
-    from steviapp_b200 import synthetic
-    nc, npt, no = synthetic.SHAPES[shape]
-    if shape in ("venice", "city"):
-        return synthetic.make_scene(shape, n_pts=npt // SAMPLE_DIV, n_obs=no // SAMPLE_DIV), no
-    return synthetic.make_scene(shape), no
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
 
-def cpu_leg(shape, steps, warmup, pcg_tol, pcg_max, threads=0):
-    """Times the CPU restatement of the reference (oracle/) on a bounded sample; returns the cpu_baseline dict.
-    value = LM iters/s extrapolated to the full workload: iters/s on the sample x (sample obs / full obs)."""
+def cpu_leg(shape, steps, warmup, pcg_tol, pcg_max, threads=0, single_thread_probe=False, scene=None, budget_s=150.0):
+    """Times the CPU restatement of the reference (oracle/) on the FULL workload -- the same scene, the same chunks of at
+    most LM_CHUNK LM iterations restarting from the initial values as the B200 arm -- with an explicit thread count
+    (all host cores by default, whatever OMP_NUM_THREADS a launcher exported).  value = LM iterations / wall second."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_py
-    sc, full_obs = sample_scene(shape)
-    nthreads = oracle_py.num_threads() if threads <= 0 else threads
+    from steviapp_b200 import synthetic
+    nthreads = host_cores() if threads <= 0 else threads
+    nthreads = oracle_py.set_max_threads(nthreads)
+    sc = synthetic.make_scene(shape) if scene is None else scene
     kw = dict(num_threads=nthreads, pcg_rel_tol=pcg_tol, pcg_max_iters=pcg_max, **FIXED)
     if warmup > 0:
-        oracle_py.Problem(sc).solve(max_iterations=min(warmup, 1), **kw)
-    p = oracle_py.Problem(sc)
-    t0 = time.perf_counter()
-    s = p.solve(max_iterations=steps, **kw)
-    dt = time.perf_counter() - t0
+        oracle_py.Problem(sc).solve(max_iterations=warmup, **kw)
+    dt, done, pcg, first = 0.0, 0, 0, None
+    asked = steps
+    while done < steps:
+        n = min(LM_CHUNK, steps - done)
+        if done and dt + dt / done * n > budget_s:   # bounded sample: stop at a chunk boundary once the budget would be exceeded
+            steps = done
+            break
+        p = oracle_py.Problem(sc)
+        t0 = time.perf_counter()
+        s = p.solve(max_iterations=n, **kw)
+        dt += time.perf_counter() - t0
+        assert s["iterations"] == n, s
+        done += n
+        pcg += s["pcg_iterations_total"]
+        if first is None:
+            first = s
     t1 = time.perf_counter()
     oracle_py.Problem(sc).evaluate(threads=nthreads)
     t_eval = time.perf_counter() - t1
-    it_s_sample = s["iterations"] / dt
-    scale = sc["n_obs"] / full_obs
-    return {
-        "value": it_s_sample * scale, "unit": UNIT, "cores": nthreads, "kind": "port",
-        "sample": (f"{shape}-shape scene at 1/{SAMPLE_DIV} of the points: {sc['n_cams']} cameras / {sc['n_pts']} points / "
-                   f"{sc['n_obs']} observations, {s['iterations']} LM iterations in {dt:.2f} s "
-                   f"({s['pcg_iterations_total']} PCG iterations); value = sample iters/s x {scale:.5f} (observation ratio)"),
-        "sample_iters_per_s": it_s_sample, "sample_seconds": dt, "pcg_iterations": s["pcg_iterations_total"],
-        "final_cost": s["final_cost"], "residual_jacobian_mobs_per_s": sc["n_obs"] / t_eval / 1e6,
+    out = {
+        "value": steps / dt, "unit": UNIT, "cores": nthreads, "kind": "port",
+        "sample": (f"the full {shape}-shape scene ({sc['n_cams']} cameras / {sc['n_pts']} points / {sc['n_obs']} observations), "
+                   f"{steps} LM iterations in solves of at most {LM_CHUNK} (each from the initial values) in {dt:.2f} s wall, "
+                   f"{pcg} PCG iterations, {nthreads} OpenMP threads; {warmup} untimed warm-up iteration(s)"
+                   + ("" if steps == asked else f"; {asked} steps were asked for, the {budget_s:.0f} s CPU budget ended the sample at {steps}")),
+        "seconds": dt, "steps": steps, "pcg_iterations": pcg,
+        "cost_history_first_solve": first["cost_history"], "pcg_iters_first_solve": first["pcg_iters_history"],
+        "residual_jacobian_mobs_per_s": sc["n_obs"] / t_eval / 1e6,
         "note": "CPU restatement of the reference (not Ceres): the reference itself needs Eigen/Ceres/Qt/LibStevi, absent here",
     }
+    if single_thread_probe and dt / steps * nthreads * 0.7 > 150.0:
+        out["single_thread"] = {"skipped": f"one 1-thread LM iteration would take > 150 s on this host ({dt / steps:.1f} s with {nthreads} threads)"}
+    elif single_thread_probe:
+        # the reference's real configuration: ceres::Solver::Options::num_threads is never set (modularsbasolver.cpp:897-924)
+        oracle_py.set_max_threads(1)
+        p = oracle_py.Problem(sc)
+        t0 = time.perf_counter()
+        s1 = p.solve(max_iterations=1, **dict(kw, num_threads=1))
+        d1 = time.perf_counter() - t0
+        oracle_py.set_max_threads(nthreads)
+        out["single_thread"] = {"value": s1["iterations"] / d1, "unit": UNIT, "cores": 1,
+                                "sample": f"1 LM iteration ({s1['pcg_iterations_total']} PCG iterations) of the same scene in {d1:.2f} s"}
+    return out
 
 
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb = cpu_leg(a.shape, max(a.steps, 1), a.warmup, a.pcg_tol, a.pcg_max_iters)
+    cb = cpu_leg(a.shape, max(a.steps, 1), min(a.warmup, 1), a.pcg_tol, a.pcg_max_iters, single_thread_probe=not a.no_single_thread)
     v = cb["value"]
+    cfg = bench_config(a)
+    cfg["linear_solver"] = "Schur complement + SCHUR_JACOBI PCG on the implicit operator (CPU oracle, OpenMP)"
+    cfg["parallelism"] = f"{cb['cores']} host threads (rank 0 only)"
+    cfg["l2"] = "n/a (CPU arm)"
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": 1e3 / v if v else None, "higher_is_better": True, "scaling": "strong",
+        "warmup": min(a.warmup, 1), "ms_per_step": 1e3 * cb["seconds"] / cb["steps"], "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": bench_config(a), "cpu_baseline": cb,
+        "config": cfg, "cpu_baseline": cb, "final_cost": cb["cost_history_first_solve"][-1],
+        "cost_history_first_solve": cb["cost_history_first_solve"],
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -171,7 +203,13 @@ ALG_BYTES = {
     "k_point_pass": 56,              # 48 A planes + 4 pt idx + 4 cam idx; C x_r rebuilt as A((X-t) x R Jr x_r) (per-camera operand and the point
                                      # from L1/L2; ~26 B/obs of Hinv / y_p per point not counted)
 }
-STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6}
+ALG_BYTES.update({
+    "k_linearize_q": 72,             # K1p + K2a: in 16 uv + 8 idx, out 48 (six point-order A planes) per observation; + 96 B per point (Hpp, gp) below
+    "k_camera_blocks": 88,           # K2b: res 16 + A 48 + Pbar 24 in (coalesced planes); 224 B per tile + 216 B per camera out (not counted)
+    "k_schur_diag": 76,              # A 48 + Pbar 24 + pt idx 4 in; + 64 B Hinv gather per observation from L2 (not counted)
+})
+ALG_BYTES_PER_POINT = {"k_linearize_q": 96}
+STAGE = {"k_residual_jacobian": 0, "k_camera_pass": 7, "k_point_pass": 6, "k_linearize_q": 5, "k_camera_blocks": 9, "k_schur_diag": 4}
 TILE_BYTES = 384 * 384 * 8           # one dense tile of the explicit reduced camera system
 
 
@@ -235,6 +273,7 @@ def run_b200(a):
     # chunks of at most LM_CHUNK iterations, every chunk restarting from the same initial values (a longer uninterrupted run
     # converges to machine precision and stops taking steps); the parameter re-upload between chunks is outside the device time.
     r = None
+    first_history = []
     ms_total = 0.0
     wall = 0.0
     done = 0
@@ -253,6 +292,7 @@ def run_b200(a):
         done += n
         if r is None:
             r = rc
+            first_history = list(rc["cost_history"])
         else:   # accumulate what the report uses
             for k in ("iterations", "pcg_iterations_total", "kernel_launches", "ms_total", "ms_linearize", "ms_schur", "ms_pcg", "ms_update"):
                 r[k] += rc[k]
@@ -288,10 +328,14 @@ def run_b200(a):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_kind = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     kern = {}
+    n_pts_local = s.sizes()["n_pts"]
     for name, stage in STAGE.items():
         ms = s.time_stage(stage, 20)
-        kern[name] = {"ms": ms, "GBps": ALG_BYTES[name] * n_obs_local / (ms * 1e-3) / 1e9, "Mobs_per_s": n_obs_local / ms / 1e3,
-                      "alg_bytes_per_launch": ALG_BYTES[name] * n_obs_local, "alg_bytes_per_obs": ALG_BYTES[name]}
+        nb = ALG_BYTES[name] * n_obs_local + ALG_BYTES_PER_POINT.get(name, 0) * n_pts_local
+        kern[name] = {"ms": ms, "GBps": nb / (ms * 1e-3) / 1e9, "Mobs_per_s": n_obs_local / ms / 1e3,
+                      "alg_bytes_per_launch": nb, "alg_bytes_per_obs": ALG_BYTES[name]}
+        if name in ALG_BYTES_PER_POINT:
+            kern[name]["alg_bytes_per_point"] = ALG_BYTES_PER_POINT[name]
     pcg_per_step = r["pcg_iterations_total"] / max(r["iterations"], 1)
     ex = s.explicit_info()
     shard = s.explicit_shard()
@@ -340,25 +384,32 @@ def run_b200(a):
         share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
     dom = max(share, key=share.get)
     traffic = None
+    traffic_source = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic_source = "profiles/traffic.json: " + str(tj.get("_source", "ncu --set full capture (dram__bytes_read.sum + dram__bytes_write.sum)")) + "; not measured in this run"
+        traffic = tj.get(
             dom + "_sparse" if kern[dom].get("tile_format") == "block-sparse panels" else dom)
         if isinstance(traffic, dict):   # persistent kernel: ncu measured one launch of 114 CG iterations; per launch of THIS run
             traffic = traffic["bytes_per_cg_iteration"] * pcg_per_step * (shard["n_own"] / max(ex["n_tiles"], 1))
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": kern[dom]["GBps"] / peak, "traffic": traffic, "peak_source": peak_kind,
+                "frac": kern[dom]["GBps"] / peak, "traffic": traffic, "traffic_source": traffic_source, "peak_source": peak_kind,
                 "alg_bytes_per_launch": kern[dom]["alg_bytes_per_launch"], "obs_per_launch": n_obs_local,
                 "share_of_step": share[dom] / (ms_total / a.steps),
-                # context only (frac stays against MEASURED_PEAKS.json): a bulk-copy ring without math streams 330 MB per pass at this
-                # rate on a B200 (scripts/bulk_ring_bench.cu, profiles/r1i_bulk_ring_bench.log); the copy peak above is read + write
-                "read_only_stream_GBps": 7429.0,
                 "kernels": {k: dict(v, frac=v["GBps"] / peak) for k, v in kern.items()}}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        cpu = cpu_leg(a.shape, 2, 1, a.pcg_tol, a.pcg_max_iters)
+        # bounded sample: 3 LM iterations of the full scene (the parity tests' count), no warm-up; the cost history is held
+        # against the GPU's below
+        cpu = cpu_leg(a.shape, 3, 0, a.pcg_tol, a.pcg_max_iters, scene=scene, budget_s=60.0)
+        gh = first_history
+        ch = cpu["cost_history_first_solve"]
+        m = min(len(gh), len(ch))
+        cpu["gpu_cost_history_first_solve"] = gh[:m]
+        cpu["max_rel_cost_diff_vs_gpu"] = max(abs(x - y) / y for x, y in zip(gh[:m], ch[:m]))
 
     if rank == 0:
         line = {

@@ -32,17 +32,29 @@ namespace sba_b200 {
 
 class GpuSBASolver;
 
+// stands in for StereoVision::Geometry::RigidBodyTransform<double> (axis-angle r, translation t) in the signature below
+struct RigidOffset {
+    double r[3] = {0.0, 0.0, 0.0};
+    double t[3] = {0.0, 0.0, 0.0};
+    bool isIdentity() const {   // the reference's own test (pinholecameraprojectormodule.cpp:58): |r| < 1e-6 and |t| < 1e-6
+        return r[0] * r[0] + r[1] * r[1] + r[2] * r[2] < 1e-12 && t[0] * t[0] + t[1] * t[1] + t[2] * t[2] < 1e-12;
+    }
+};
+
 // Drop-in for PinholeCamProjModule: one instance per Camera datablock (= one
 // camera model: f, pp, k, t, B blocks shared by all its images).
 class GpuPinholeProjectorModule {
 public:
     GpuPinholeProjectorModule(GpuSBASolver* solver, int32_t model) : _solver(solver), _model(model) {}
 
-    // same argument meaning as ProjectorModule::addProjectionCostFunction; returns false when the
-    // module was not set up (pinholecameraprojectormodule.cpp:253-255).  uv = pixel, stiffness = 2x2 row-major.
-    // The offset / lever-arm variants of the reference signature are "next" rows.
+    // the full signature of ProjectorModule::addProjectionCostFunction (modularsbasolver.h:169-177), same argument
+    // meaning; returns false when the module was not set up (pinholecameraprojectormodule.cpp:253-255), when a block
+    // was not registered, or when the pose was registered under another camera model than this module's.
+    // uv = pixel, stiffness = 2x2 row-major.
     inline bool addProjectionCostFunction(double* pointData, double* poseOrientation, double* posePosition,
-                                          const double uv[2], const double stiffness[4]);
+                                          const double uv[2], const double stiffness[4],
+                                          const RigidOffset& offset = RigidOffset(),
+                                          double* leverArmOrientation = nullptr, double* leverArmPosition = nullptr);
 
     int32_t model() const { return _model; }
 
@@ -166,11 +178,15 @@ private:
         }
         for (size_t i = 0; i < _ptPtr.size(); i++) std::memcpy(&_x[3 * i], _ptPtr[i], 3 * sizeof(double));
     }
-    bool addObservation(double* pt, double* rAxis, double* t, const double uv[2], const double W[4]) {
+    bool addObservation(int32_t model, double* pt, double* rAxis, double* t, const double uv[2], const double W[4]) {
         auto ip = _ptIndex.find(pt);
         auto ic = _poseIndex.find(rAxis);
         if (ip == _ptIndex.end() || ic == _poseIndex.end() || _poseT[ic->second] != t) {
             _err = "addProjectionCostFunction: parameter block was not registered";
+            return false;
+        }
+        if (_poseModel[ic->second] != model) {   // in the reference the module OWNS the intrinsic blocks of its Camera
+            _err = "addProjectionCostFunction: the pose was registered under another camera model than this module's";
             return false;
         }
         const bool identity = !W || (W[0] == 1.0 && W[1] == 0.0 && W[2] == 0.0 && W[3] == 1.0);
@@ -203,9 +219,16 @@ private:
 
 inline bool GpuPinholeProjectorModule::addProjectionCostFunction(double* pointData, double* poseOrientation,
                                                                  double* posePosition, const double uv[2],
-                                                                 const double stiffness[4]) {
+                                                                 const double stiffness[4], const RigidOffset& offset,
+                                                                 double* leverArmOrientation, double* leverArmPosition) {
     if (!_solver) return false;
-    return _solver->addObservation(pointData, poseOrientation, posePosition, uv, stiffness);
+    if (!offset.isIdentity() || leverArmOrientation != nullptr || leverArmPosition != nullptr) {
+        // PoseTransformCost / LeverArmCost / PoseTransformLeverArmCost (pinholecameraprojectormodule.cpp:147-214): refuse
+        // rather than silently solving another problem (the reference's own failure convention is `false`)
+        _solver->_err = "addProjectionCostFunction: sensor offsets / lever arms are not routed to the GPU engine by this adaptor";
+        return false;
+    }
+    return _solver->addObservation(_model, pointData, poseOrientation, posePosition, uv, stiffness);
 }
 
 }  // namespace sba_b200

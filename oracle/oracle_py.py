@@ -167,3 +167,10 @@ def uv_from_dir(xn, intr10):
 
 def num_threads():
     return load().oracle_num_threads()
+
+
+def set_max_threads(n=0):
+    """Caps the OpenMP team at n threads (0 = all online processors) whatever OMP_NUM_THREADS the launcher exported."""
+    lib = load()
+    lib.oracle_set_max_threads.restype = C.c_int
+    return lib.oracle_set_max_threads(int(n))

@@ -631,6 +631,19 @@ extern "C" {
 
 int oracle_num_threads(void) { return nthreads(0); }
 
+// Upper bound of the OpenMP team for every later call (overrides an OMP_NUM_THREADS inherited from a launcher: torchrun
+// exports OMP_NUM_THREADS=1 to its workers).  n <= 0: number of online processors.
+int oracle_set_max_threads(int n) {
+#ifdef _OPENMP
+    if (n <= 0) n = omp_get_num_procs();
+    omp_set_num_threads(n);
+    return omp_get_max_threads();
+#else
+    (void)n;
+    return 1;
+#endif
+}
+
 void oracle_default_options(oracle_options* o) {
     // set by the reference: modularsbasolver.cpp:897-924 (tolerances 1e-8 / 1e-10);
     // everything else Ceres defaults [external].
@@ -1000,8 +1013,11 @@ int oracle_solve(oracle_problem* p, const oracle_options* opt, oracle_summary* s
                 std::copy(r0.begin(), r0.end(), p->cam_r); std::copy(t0v.begin(), t0v.end(), p->cam_t); std::copy(x0.begin(), x0.end(), p->pts);
             }
         }
-        if (!accepted) {
-            // StepRejected / StepIsInvalid
+        if (!step_valid) {
+            // LevenbergMarquardtStrategy::StepIsInvalid [external]: the radius is halved, decrease_factor is left alone
+            radius *= 0.5;
+        } else if (!accepted) {
+            // StepRejected
             radius = radius / decrease_factor;
             decrease_factor *= 2.0;
         }

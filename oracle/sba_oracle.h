@@ -135,6 +135,9 @@ int oracle_triangulate(const oracle_problem* cams, int32_t n_points,
                        uint8_t* ok_out);
 
 int oracle_num_threads(void);
+/* caps the OpenMP team of every later call at n threads (n <= 0: all online processors), whatever OMP_NUM_THREADS the
+ * process inherited; returns the new maximum */
+int oracle_set_max_threads(int n);
 
 #ifdef __cplusplus
 }

@@ -156,6 +156,8 @@ struct DevProblem {
     double* prior_A;      // 9*Nprior (sorted by group)
     double* prior_b;      // 3*Nprior
     double* prior_res;    // 3*Nprior
+    int32_t Nlonely;      // free points that carry priors but no observation (a ground-control landmark no image sees): they head
+    int32_t* lonely_pt;   //   no q slot, so the back-substitution handles them in a list kernel (dp = -Hinv gp)
     // normal-equation blocks
     double* Hpp;          // 8*Np AoS: packed symmetric 3x3 (6) + pad, undamped
     double* gp;           // 4*Np AoS

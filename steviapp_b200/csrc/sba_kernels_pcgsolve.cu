@@ -573,10 +573,14 @@ __global__ void __launch_bounds__(PS_THREADS, 1) k_pcg_solve(DevProblem P, doubl
 }
 
 static int ps_grid_blocks() {
-    static int blocks = -1;
-    if (blocks < 0) {
-        int dev = 0, coop = 0, sms = 0, per_sm = 0, smem_max = 0;
-        cudaGetDevice(&dev);
+    static int blocks_of[64];   // per device ordinal (0 = not probed yet, -1 = unavailable)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& cached = blocks_of[dev & 63];
+    if (cached != 0) return cached < 0 ? 0 : cached;
+    int blocks = -1;
+    {
+        int coop = 0, sms = 0, per_sm = 0, smem_max = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
@@ -589,6 +593,7 @@ static int ps_grid_blocks() {
             blocks = sms;
         cudaGetLastError();
     }
+    cached = blocks > 0 ? blocks : -1;
     return blocks;
 }
 int pcg_solve_grid() { return ps_grid_blocks(); }
@@ -599,13 +604,13 @@ bool launch_pcg_solve(const DevProblem& P, double tol2, int max_iters, cudaStrea
     DevProblem Pc = P;
     // share of the rank's tiles kept L2-resident across the CG iterations (SBA_PS_L2_MB, default 80 MB of the 126 MB L2),
     // as the same number of leading 12 KB half groups of every CTA's run
-    static const double l2_mb = std::getenv("SBA_PS_L2_MB") ? std::atof(std::getenv("SBA_PS_L2_MB")) : 80.0;
+    const double l2_mb = std::getenv("SBA_PS_L2_MB") ? std::atof(std::getenv("SBA_PS_L2_MB")) : 80.0;
     int pin_hg = (int)(l2_mb * 1e6 / ((double)P.ps_grid * PS_STAGE_BYTES));
     if (P.sp_on) pin_hg = (int)(l2_mb * 1e6 / (double)P.ps_grid);   // bytes of every run
     // SBA_PS_MODE: bit 0 ring prefetch during the barriers / fold, bit 1 L2-resident share interleaved over the run
     // (block-sparse panels only, default both on: measured 57.2 -> 56.2 us per CG iteration on the Venice shape; the dense-tile
     // variant ignores it -- neither changed its time).  pin_f16 / 65536 = share of the bytes behind the prefetched ones to keep.
-    static const int ps_mode_env = std::getenv("SBA_PS_MODE") ? std::atoi(std::getenv("SBA_PS_MODE")) : -1;
+    const int ps_mode_env = std::getenv("SBA_PS_MODE") ? std::atoi(std::getenv("SBA_PS_MODE")) : -1;
     const int ps_mode = ps_mode_env >= 0 ? ps_mode_env : 3;
     const double frac = P.sp_on ? l2_mb * 1e6 / std::max((double)P.sp_bytes - ((ps_mode & 1) ? (double)P.ps_grid * SP_RING_BYTES : 0.0), 1.0) : 0.0;
     int pin_f16 = (int)(std::min(std::max(frac, 0.0), 1.0) * 65536.0);

@@ -262,9 +262,16 @@ __global__ void __launch_bounds__(256) k_point_hinv_g(DevProblem P) {
     st2(o, h01.x * g01.x + h01.y * g01.y + h23.x * g23.x, h01.y * g01.x + h23.y * g01.y + h45.x * g23.x);
     st2(o + 2, h23.x * g01.x + h45.x * g01.y + h45.y * g23.x, 0.0);
 }
+// back-substitution of the free points that carry priors but no observation (no q slot): dp = -Hinv gp
+__global__ void k_point_lonely(DevProblem P) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= P.Nlonely) return;
+    finish_point_pass<2>(P, P.lonely_pt[k], 0.0, 0.0, 0.0);
+}
 void launch_point_pass(const DevProblem& P, const double* x, int mode, cudaStream_t st, bool table_ready) {
     if (P.Np == 0) return;
     if (mode == 1) { k_point_hinv_g<<<cdiv(P.Np, 256), 256, 0, st>>>(P); return; }
+    if (mode == 2 && P.Nlonely) k_point_lonely<<<cdiv(P.Nlonely, 128), 128, 0, st>>>(P);
     if (!table_ready) launch_cam_vec(P, x, st);
     // shared-memory table variant when the table fits (persistent blocks, 1 or 2 per SM)
     static int sms = 0, smem_max = 0;

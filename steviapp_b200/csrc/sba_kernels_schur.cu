@@ -80,9 +80,13 @@ __global__ void k_prior_blocks(DevProblem P, int cameras) {
     if (kind == 0) {
         double* Hp = P.Hpp + 8 * (size_t)idx;
         double* gp = P.gp + 4 * (size_t)idx;
+        // a point without observations heads no q slot, so k_linearize_q never rewrites its blocks: the priors ARE its
+        // blocks (assigned, not accumulated -- otherwise they would grow by A^T A with every linearisation)
+        const bool unobserved = P.pt_off[idx] == P.pt_off[idx + 1];
 #pragma unroll
-        for (int i = 0; i < 6; i++) Hp[i] += H[i];
-        gp[0] += gg[0]; gp[1] += gg[1]; gp[2] += gg[2];
+        for (int i = 0; i < 6; i++) Hp[i] = (unobserved ? 0.0 : Hp[i]) + H[i];
+#pragma unroll
+        for (int i = 0; i < 3; i++) gp[i] = (unobserved ? 0.0 : gp[i]) + gg[i];
     } else {
         const int off = kind == 1 ? 0 : 3;
         double* Hc = P.Hcc + 21 * (size_t)idx;

@@ -33,6 +33,18 @@ int main() {
             std::fprintf(stderr, "an unregistered point block was accepted\n");
             return 1;
         }
+        {   // the other branches of the reference signature (pinholecameraprojectormodule.cpp:147-214) and a foreign camera model
+            // must be refused with `false`, never forwarded as a plain observation
+            double probe[3] = {1, 2, 30}, la_r[3] = {0, 0, 0}, la_t[3] = {0, 0, 0};
+            solver.registerPoint(probe);
+            RigidOffset off;
+            off.t[0] = 0.1;
+            if (cam.addProjectionCostFunction(probe, rAxis, pos, uv[0], I2, off)) { std::fprintf(stderr, "a non-identity offset was accepted\n"); return 1; }
+            if (cam.addProjectionCostFunction(probe, rAxis, pos, uv[0], I2, RigidOffset(), la_r, la_t)) { std::fprintf(stderr, "a lever arm was accepted\n"); return 1; }
+            GpuPinholeProjectorModule other = solver.addCameraModel(2.0 * f, pp, k, t2, B);
+            if (other.addProjectionCostFunction(probe, rAxis, pos, uv[0], I2)) { std::fprintf(stderr, "a pose of another camera model was accepted\n"); return 1; }
+            if (solver.lastError().empty()) return 1;
+        }
         for (int i = 0; i < 5; i++) {
             solver.registerPoint(pts[i], /*fixed*/ part == 1);
             if (!cam.addProjectionCostFunction(pts[i], rAxis, pos, uv[i], i % 2 ? I2 : nullptr)) {

@@ -444,3 +444,141 @@ def test_intrinsics_jacobian(oracle, kw, with_info):
     assert j.shape == jo.shape and np.abs(j[:, :, 8:]).max() == 0.0
     for c in range(8):
         assert relerr(j[:, :, c], jo[:, :, c]) < TOL_J, c
+
+
+def _with_priors(sc, rng):
+    """Pose priors on rAxis / t (imagealignementsbamodule.cpp:256-286) and point priors, all with FULL non-symmetric
+    stiffness matrices (FixedSizeNormalPrior<3,3>::Evaluate is r = A (x - b), J = A row-major, fixedsizenormalprior.h:75-112);
+    two priors on one block, a prior on the fixed camera (skipped in the blocks), a prior on a fixed point."""
+    sc = dict(sc)
+    kind = [1, 2, 1, 2, 2, 1, 0, 0, 0, 0]
+    index = [3, 3, 7, 7, 7, 0, 11, 11, 40, 5]
+    A = rng.normal(size=(len(kind), 3, 3)) * 3.0 + 2.0 * np.eye(3)
+    b = np.empty((len(kind), 3))
+    for i, (k, j) in enumerate(zip(kind, index)):
+        x = sc["pts_true"][j] if k == 0 else (sc["raxis_true"][j] if k == 1 else sc["t_true"][j])
+        b[i] = x + rng.normal(0, 0.02, 3)
+    sc["pt_fixed"] = sc["pt_fixed"].copy(); sc["pt_fixed"][5] = 1
+    sc["prior_kind"] = np.concatenate([sc["prior_kind"], np.array(kind, np.int32)])
+    sc["prior_index"] = np.concatenate([sc["prior_index"], np.array(index, np.int32)])
+    sc["prior_A"] = np.concatenate([sc["prior_A"], A.reshape(-1, 9)])
+    sc["prior_b"] = np.concatenate([sc["prior_b"], b])
+    return sc
+
+
+@pytest.mark.parametrize("operator_mode", [0, 2])
+def test_pose_priors_and_full_prior_matrices(oracle, operator_mode):
+    sc = _with_priors(synthetic.make_scene("small"), np.random.default_rng(17))
+    p = oracle.Problem(sc)
+    o = p.normal_blocks()
+    eo = p.evaluate()
+    s, _ = gpu_solver(sc, operator_mode=operator_mode)
+    e = s.evaluate(jacobians=False)
+    assert abs(e["cost"] - eo["cost"]) <= 1e-12 * eo["cost"]
+    g = s.normal_blocks()
+    for k in ("gc", "gp", "Hcc", "Hpp"):
+        assert relerr(g[k], o[k]) < 1e-11, k
+    so = oracle.Problem(sc).solve(max_iterations=5, num_threads=1, **FIXED_ITERS)
+    out = s.solve(max_iterations=5, **FIXED_ITERS)
+    assert out["pcg_iters_history"][1] == so["pcg_iters_history"][1]
+    for a, b in zip(out["cost_history"], so["cost_history"]):
+        assert abs(a - b) <= TOL_COST * max(b, 1.0)
+
+
+def test_prior_only_point(oracle):
+    """A free point that carries priors but no observation (a ground-control landmark no image sees): its blocks are the
+    priors alone -- after ANY number of linearisations -- and the LM moves it onto the prior like the oracle does."""
+    sc = synthetic.make_scene("small")
+    lonely = 17
+    keep = sc["obs_pt"] != lonely
+    for k in ("obs_cam", "obs_pt", "obs_uv"):
+        sc[k] = np.ascontiguousarray(sc[k][keep])
+    sc["n_obs"] = int(keep.sum())
+    rng = np.random.default_rng(2)
+    A = rng.normal(size=(2, 3, 3)) + 3.0 * np.eye(3)
+    sc["prior_kind"] = np.concatenate([sc["prior_kind"], np.zeros(2, np.int32)])
+    sc["prior_index"] = np.concatenate([sc["prior_index"], np.full(2, lonely, np.int32)])
+    sc["prior_A"] = np.concatenate([sc["prior_A"], A.reshape(-1, 9)])
+    sc["prior_b"] = np.concatenate([sc["prior_b"], sc["pts_true"][lonely] + rng.normal(0, 0.01, (2, 3))])
+    p = oracle.Problem(sc)
+    o = p.normal_blocks()
+    s, (_, _, pts) = gpu_solver(sc)
+    for _ in range(3):                       # the blocks must not grow with repeated linearisations
+        g = s.normal_blocks()
+        for k in ("gp", "Hpp"):
+            assert relerr(g[k], o[k]) < 1e-11, k
+    so = p.solve(max_iterations=3, num_threads=1, **FIXED_ITERS)
+    out = s.solve(max_iterations=3, **FIXED_ITERS)
+    for a, b in zip(out["cost_history"], so["cost_history"]):
+        assert abs(a - b) <= TOL_COST * max(b, 1.0)
+    assert np.abs(pts[lonely] - p.pts.reshape(-1, 3)[lonely]).max() < 1e-9
+    assert np.abs(pts[lonely] - sc["pts"][lonely]).max() > 1e-3      # it did move
+
+
+def test_iteration_callback_reports_and_aborts():
+    """sba_set_iteration_callback = ModularSBASolverIterationCallback (modularsbasolver.cpp:30-56): called once per LM
+    iteration with the state the summary records; a non-zero return stops the solve after that iteration."""
+    sc = synthetic.make_scene("small")
+    s, _ = gpu_solver(sc)
+    seen = []
+    s.set_iteration_callback(lambda info: seen.append(dict(info)) and False)
+    out = s.solve(max_iterations=5, **FIXED_ITERS)
+    assert [i["iteration"] for i in seen] == [1, 2, 3, 4, 5]
+    for i in seen:
+        k = i["iteration"]
+        assert i["cost"] == out["cost_history"][k] and i["radius"] == out["radius_history"][k]
+        assert i["pcg_iterations"] == out["pcg_iters_history"][k]
+        assert i["step_valid"] == 1
+        if i["step_accepted"]:
+            assert abs(i["cost_change"] - (out["cost_history"][k - 1] - out["cost_history"][k])) <= 1e-9 * out["cost_history"][k - 1]
+    s.close()
+    s, _ = gpu_solver(sc)
+    calls = []
+    s.set_iteration_callback(lambda info: calls.append(info["iteration"]) or info["iteration"] == 2)
+    out2 = s.solve(max_iterations=5, **FIXED_ITERS)
+    assert calls == [1, 2] and out2["iterations"] == 2
+    assert out2["cost_history"] == out["cost_history"][:3]
+    s.set_iteration_callback(None)
+    out3 = s.solve(max_iterations=2, copy_params=False, **FIXED_ITERS)
+    assert calls == [1, 2] and out3["iterations"] == 2
+
+
+def test_triangulation_mixed_scene_100k_points(oracle):
+    """K5 on a mixed plane / spherical scene with > 1e5 points against the oracle's DLT."""
+    sc = synthetic.make_scene(None, n_cams=240, n_pts=120_000, n_obs=600_000, seed=21, mixed=True)
+    sc["raxis"], sc["t"] = sc["raxis_true"].copy(), sc["t_true"].copy()
+    order = np.argsort(sc["obs_pt"], kind="stable")
+    view_cam = sc["obs_cam"][order]; view_uv = sc["obs_uv"][order]
+    view_off = np.concatenate([[0], np.cumsum(np.bincount(sc["obs_pt"], minlength=sc["n_pts"]))]).astype(np.int32)
+    xo, oko = oracle.Problem(sc).triangulate(view_off, view_cam, view_uv)
+    s, _ = gpu_solver(sc)
+    x, ok, ms = s.triangulate(view_off, view_cam, view_uv)
+    assert ok.all() and oko.all()
+    assert relerr(x, xo) < 1e-10
+    assert np.median(np.abs(x - sc["pts_true"]).max(axis=1)) < 0.05
+
+
+@pytest.mark.parametrize("mixed", [False, True])
+def test_venice_scale_against_oracle(oracle, mixed):
+    """The north-star target itself: the full Venice-shape scene (1778 / 993 923 / 5 001 946) on the GPU against the CPU
+    oracle on the same arrays -- all residuals and Jacobians at 1e-12, and the cost history of 3 fixed LM iterations at
+    1e-8 with equal PCG iteration counts (+-1 at the 1e-10 exit)."""
+    oracle.set_max_threads(0)
+    sc = synthetic.make_scene("venice", mixed=mixed)
+    p = oracle.Problem(sc)
+    o = p.evaluate(threads=0)
+    s, _ = gpu_solver(sc, pcg_check_every=4)
+    e = s.evaluate()
+    assert e["ok"] and o["ok"] and e["residuals"].shape == (5001946, 2)
+    assert relerr(e["residuals"], o["residuals"]) < TOL_J
+    assert relerr(e["jac_cam"], o["jac_cam"]) < TOL_J
+    assert relerr(e["jac_pt"], o["jac_pt"]) < TOL_J
+    assert abs(e["cost"] - o["cost"]) <= 1e-12 * o["cost"]
+    del e, o
+    so = p.solve(max_iterations=3, num_threads=0, **FIXED_ITERS)
+    out = s.solve(max_iterations=3, **FIXED_ITERS)
+    assert out["iterations"] == so["iterations"] == 3
+    for a, b in zip(out["cost_history"], so["cost_history"]):
+        assert abs(a - b) <= TOL_COST * b
+    assert abs(out["final_cost"] - so["final_cost"]) <= TOL_COST * so["final_cost"]
+    assert all(abs(a - b) <= 1 for a, b in zip(out["pcg_iters_history"][1:], so["pcg_iters_history"][1:]))
