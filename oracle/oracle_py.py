@@ -174,3 +174,101 @@ def set_max_threads(n=0):
     lib = load()
     lib.oracle_set_max_threads.restype = C.c_int
     return lib.oracle_set_max_threads(int(n))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# extended problem class (sba_oracle_ext.cpp): free intrinsics, sensor offsets / lever arms, UV <-> UV factors, covariance
+class OracleExtProblem(C.Structure):
+    _fields_ = [
+        ("base", OracleProblem),
+        ("intr_rw", C.c_void_p), ("intr_fixed_mask", C.c_void_p),
+        ("n_intr_priors", C.c_int32), ("ip_model", C.c_void_p), ("ip_block", C.c_void_p), ("ip_A", C.c_void_p), ("ip_b", C.c_void_p),
+        ("cam_offset", C.c_void_p), ("cam_mount", C.c_void_p),
+        ("n_mounts", C.c_int32), ("mount_b", C.c_void_p), ("mount_l", C.c_void_p), ("mount_fixed", C.c_void_p),
+        ("n_pairs", C.c_int32), ("pair_cam", C.c_void_p), ("pair_uv", C.c_void_p), ("pair_info", C.c_void_p),
+        ("loss_kind", C.c_int32), ("loss_a", C.c_double),
+    ]
+
+
+LOSS = {None: 0, "none": 0, "huber": 1, "cauchy": 2, "arctan": 3}
+
+
+class ExtProblem(Problem):
+    """Scene dict as for Problem plus the optional keys: intr_fixed_mask (n_models uint8; absent = intrinsics constant),
+    intr_prior_model / _block / _A (n,9) / _b (n,3), cam_offset (n_cams,6), cam_mount (n_cams int32, -1 none), mount_b /
+    mount_l (n_mounts,3), mount_fixed, pair_cam (n,2), pair_uv (n,4), pair_info (n,8), loss ("huber" | "cauchy" | "arctan"), loss_a."""
+
+    def __init__(self, scene):
+        super().__init__(scene)
+        g = lambda k, dt: None if scene.get(k) is None else np.ascontiguousarray(scene[k], dtype=dt).copy()
+        self.intr_mask = g("intr_fixed_mask", np.uint8)
+        self.ip_model = g("intr_prior_model", np.int32); self.ip_block = g("intr_prior_block", np.int32)
+        self.ip_A = g("intr_prior_A", np.float64); self.ip_b = g("intr_prior_b", np.float64)
+        self.cam_offset = g("cam_offset", np.float64); self.cam_mount = g("cam_mount", np.int32)
+        self.mount_b = g("mount_b", np.float64); self.mount_l = g("mount_l", np.float64); self.mount_fixed = g("mount_fixed", np.uint8)
+        self.pair_cam = g("pair_cam", np.int32); self.pair_uv = g("pair_uv", np.float64); self.pair_info = g("pair_info", np.float64)
+        n_ip = 0 if self.ip_model is None else self.ip_model.size
+        n_mt = 0 if self.mount_b is None else self.mount_b.size // 3
+        n_pr = 0 if self.pair_cam is None else self.pair_cam.size // 2
+        self.n_mounts, self.n_pairs = n_mt, n_pr
+        self.e = OracleExtProblem(self.c, _p(self.intr) if self.intr_mask is not None else None, _p(self.intr_mask),
+                                  n_ip, _p(self.ip_model), _p(self.ip_block), _p(self.ip_A), _p(self.ip_b),
+                                  _p(self.cam_offset), _p(self.cam_mount), n_mt, _p(self.mount_b), _p(self.mount_l), _p(self.mount_fixed),
+                                  n_pr, _p(self.pair_cam), _p(self.pair_uv), _p(self.pair_info),
+                                  LOSS[scene.get("loss")], float(scene.get("loss_a", 1.0)))
+
+    def layout(self):
+        lib = load()
+        n = C.c_int32()
+        mb = np.zeros(max(self.intr.size // 10, 1), dtype=np.int32); tb = np.zeros(max(self.n_mounts, 1), dtype=np.int32)
+        lib.oracle_ext_layout(C.byref(self.e), C.byref(n), _p(mb), _p(tb), None)
+        live = np.zeros(6 * n.value, dtype=np.uint8)
+        lib.oracle_ext_layout(C.byref(self.e), C.byref(n), _p(mb), _p(tb), _p(live))
+        return {"n_ext": n.value, "model_block": mb[:self.intr.size // 10], "mount_block": tb[:self.n_mounts], "live": live.astype(bool)}
+
+    def evaluate(self, threads=0, jac=True):
+        lib = load()
+        cost = C.c_double()
+        n, k = self.n_obs, self.n_pairs
+        r = np.empty((n, 2)); jc = np.empty((n, 2, 6)); jp = np.empty((n, 2, 3)); ji = np.empty((n, 2, 10)); jl = np.empty((n, 2, 6))
+        pr = np.empty((k, 4)); pj = np.empty((k, 4, 32))
+        rc = lib.oracle_ext_evaluate(C.byref(self.e), C.byref(cost), _p(r), _p(jc), _p(jp), _p(ji), _p(jl), _p(pr), _p(pj))
+        return {"cost": cost.value, "ok": rc == 0, "residuals": r, "jac_cam": jc, "jac_pt": jp, "jac_intr": ji, "jac_lever": jl,
+                "pair_residuals": pr, "pair_jac": pj}
+
+    def _options(self, kw):
+        lib = load()
+        o = OracleOptions()
+        lib.oracle_default_options(C.byref(o))
+        for k, v in kw.items():
+            if not hasattr(o, k):
+                raise AttributeError(k)
+            setattr(o, k, v)
+        return o
+
+    def reduced(self, radius=0.0, **kw):
+        lib = load()
+        n = 6 * self.layout()["n_ext"]
+        S = np.empty((n, n)); rhs = np.empty(n)
+        o = self._options(kw)
+        rc = lib.oracle_ext_reduced(C.byref(self.e), C.byref(o), C.c_double(radius), _p(S), _p(rhs))
+        assert rc == 0, rc
+        return S, rhs
+
+    def point_covariance(self):
+        lib = load()
+        cov = np.empty((self.n_pts, 3, 3))
+        rc = lib.oracle_ext_point_covariance(C.byref(self.e), _p(cov))
+        assert rc == 0, rc
+        return cov
+
+    def solve(self, **kw):
+        lib = load()
+        o = self._options(kw)
+        s = OracleSummary()
+        lib.oracle_ext_solve(C.byref(self.e), C.byref(o), C.byref(s))
+        n = min(s.iterations, MAX_HISTORY - 1) + 1
+        return {"status": s.status, "iterations": s.iterations, "successful_steps": s.successful_steps,
+                "pcg_iterations_total": s.pcg_iterations_total, "initial_cost": s.initial_cost, "final_cost": s.final_cost,
+                "cost_history": list(s.cost_history[:n]), "radius_history": list(s.radius_history[:n]),
+                "pcg_iters_history": list(s.pcg_iters_history[:n]), "seconds_total": s.seconds_total}

@@ -134,6 +134,45 @@ int oracle_triangulate(const oracle_problem* cams, int32_t n_points,
                        const double* view_uv, int num_threads, double* xyz_out,
                        uint8_t* ok_out);
 
+/* ---- extended problem class (sba_oracle_ext.cpp): free intrinsic blocks, sensor offsets / lever arms, UV <-> UV factors
+ * under a robust loss, point covariances.  Dense reduced system: scenes of up to a few hundred cameras. ---- */
+typedef struct {
+    oracle_problem base;              /* cameras, points, projection observations, 3-D priors as above */
+    double* intr_rw;                  /* NULL: intrinsics constant; else the same n_models*10 array as base.intrinsics, updated in place */
+    const uint8_t* intr_fixed_mask;   /* n_models or NULL (= all constant): bit k set -> block k constant, k = 0 f, 1 pp, 2 k, 3 t, 4 B
+                                         (SetParameterBlockConstant rules of pinholecameraprojectormodule.cpp:356-507) */
+    int32_t n_intr_priors;            /* FixedSizeNormalPrior<n,n> on an intrinsic block (pinholecameraprojectormodule.cpp:327-345,365-378,...) */
+    const int32_t* ip_model;          /* n_intr_priors */
+    const int32_t* ip_block;          /* n_intr_priors: block index as above */
+    const double* ip_A;               /* 9 per prior: dim x dim row-major in the leading entries */
+    const double* ip_b;               /* 3 per prior */
+    const double* cam_offset;         /* 6*n_cams (r_off, t_off): constant sensor -> body transform, or NULL (identity) */
+    const int32_t* cam_mount;         /* n_cams or NULL: lever-arm block of the camera, -1 = none */
+    int32_t n_mounts;
+    double* mount_b;                  /* 3*n_mounts boresight (axis-angle), updated in place */
+    double* mount_l;                  /* 3*n_mounts lever arm, updated in place */
+    const uint8_t* mount_fixed;       /* n_mounts or NULL */
+    int32_t n_pairs;                  /* UV <-> UV factors (UV2UVCost) */
+    const int32_t* pair_cam;          /* 2*n_pairs */
+    const double* pair_uv;            /* 4*n_pairs: uv1, uv2 */
+    const double* pair_info;          /* 8*n_pairs: info1, info2 row-major 2x2, or NULL */
+    int32_t loss_kind;                /* on the factors: 0 none, 1 Huber, 2 Cauchy, 3 Arctan (correspondencessetsbamodule.cpp:2459-2471) */
+    double loss_a;                    /* scale (the reference passes 1) */
+} oracle_ext_problem;
+
+/* layout of the reduced system: n_ext extended cameras; first block of every model (-1: all its blocks constant), block of
+ * every mounting (-1: constant), live flag of every column (6*n_ext) */
+int oracle_ext_layout(const oracle_ext_problem* q, int32_t* n_ext, int32_t* model_block, int32_t* mount_block, uint8_t* live);
+/* residuals 2*n_obs, jac_cam 12, jac_pt 6, jac_intr 20, jac_lever 12 per observation; pair_res 4, pair_jac 4 x 32 per factor
+ * (raw, before the loss; columns pose1 6, pose2 6, intrinsics of camera 1 10, of camera 2 10); cost = 1/2 (sum r^2 + sum rho) */
+int oracle_ext_evaluate(const oracle_ext_problem* q, double* cost, double* residuals, double* jac_cam, double* jac_pt,
+                        double* jac_intr, double* jac_lever, double* pair_res, double* pair_jac);
+/* dense reduced system (6 n_ext)^2 and rhs at the current point for a trust-region radius (<= 0: undamped) */
+int oracle_ext_reduced(const oracle_ext_problem* q, const oracle_options* opt, double radius, double* S, double* rhs);
+/* 3x3 marginal covariance of every point block (ModularSBASolver::std_step) */
+int oracle_ext_point_covariance(const oracle_ext_problem* q, double* cov9);
+int oracle_ext_solve(oracle_ext_problem* q, const oracle_options* o, oracle_summary* s);
+
 int oracle_num_threads(void);
 /* caps the OpenMP team of every later call at n threads (n <= 0: all online processors), whatever OMP_NUM_THREADS the
  * process inherited; returns the new maximum */
