@@ -133,6 +133,33 @@ const char* sba_create_error(void);
  * (FixedParameter::CameraInternal, :358-361,406-408). */
 int sba_set_intrinsics(sba_solver* s, int32_t n_models, const double* intr10);
 
+/* Camera models with FREE intrinsic blocks -- the reference's default: PinholeCamProjModule::init adds the
+ * five blocks f[1], pp[2], k[3], t[2], B[2] per Camera and holds a block constant only when the Camera is fixed,
+ * FixedParameter::CameraInternal is set or the distortion model is switched off
+ * (sbamodules/pinholecameraprojectormodule.cpp:302-533; constant branches :358-361,404-408,456-460,503-507).
+ * intr10 stays owned by the caller and is UPDATED IN PLACE by sba_solve (as Ceres updates the module's blocks);
+ * fixed_mask[m] bit k set -> block k of model m constant (k = 0 f, 1 pp, 2 k, 3 t, 4 B); NULL = everything constant.
+ * The B block has an identically zero Jacobian (the skew is built from the tangential block,
+ * pinholecameraprojectormodule.h:46-47): its step is zero whether it is free or not.  Free blocks join the reduced camera
+ * system as pseudo-cameras (sba_shared_info); they need the explicit reduced system (operator_mode 0 or 3). */
+int sba_set_intrinsics_blocks(sba_solver* s, int32_t n_models, double* intr10, const uint8_t* fixed_mask);
+/* FixedSizeNormalPrior<n,n> on an intrinsic block (pinholecameraprojectormodule.cpp:327-345,365-378,421-438,470-485,517-531):
+ * r = A (x - b), A = dim x dim row-major in the leading entries of its 9 doubles, b in the leading entries of its 3. */
+int sba_add_intrinsics_priors(sba_solver* s, int32_t n, const int32_t* model, const int32_t* block, const double* A9, const double* b3);
+/* Constant sensor -> body offsets: offset6 = n_cams x (r_off[3] axis-angle, t_off[3]); the projection
+ * cost is evaluated at pose * offset (PoseTransformCost, pinholecameraprojectormodule.cpp:23,197-214;
+ * costfunctors/posedecoratorfunctors.h:628-700).  NULL = identity for every camera.  Call after sba_set_poses. */
+int sba_set_sensor_offsets(sba_solver* s, const double* offset6);
+/* Free boresight / lever-arm blocks (LeverArmCost / PoseTransformLeverArmCost, pinholecameraprojectormodule.cpp:21,25,60-99,
+ * 147-166; costfunctors/posedecoratorfunctors.h:148-264): sensor2world = (pose * offset) * (boresight, leverArm).
+ * boresight / lever are n_mounts x 3, caller-owned, UPDATED IN PLACE; cam_mount[c] = mounting of camera c or -1;
+ * fixed[k] != 0 holds mounting k constant.  Call after sba_set_poses. */
+int sba_set_lever_arms(sba_solver* s, int32_t n_mounts, double* boresight, double* lever, const uint8_t* fixed, const int32_t* cam_mount);
+/* layout of the reduced camera system after finalize: n_ext extended cameras (6 columns each) = the poses followed by two
+ * pseudo-cameras [f ppx ppy k1 k2 k3] [t1 t2 - - - -] per free model and one [boresight | leverArm] per free mounting;
+ * model_block[m] / mount_block[k] = first pseudo-camera or -1.  Any pointer may be NULL.  Measurement / test hook. */
+int sba_shared_info(const sba_solver* s, int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block);
+
 /* Pose blocks: getNodeForFrame + initManagedParameters
  * (modularsbasolver.cpp:233-306,804-870).  raxis/t are 3*n AoS, caller-owned,
  * updated in place by sba_solve.  fixed -> SetParameterBlockConstant. */

@@ -27,6 +27,7 @@ EXPORTS = [
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
     "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
     "sba_pushbroom_equivalent_uv",
+    "sba_set_intrinsics_blocks", "sba_add_intrinsics_priors", "sba_set_sensor_offsets", "sba_set_lever_arms", "sba_shared_info",
 ]
 
 
@@ -113,6 +114,11 @@ def load():
     lib.sba_explicit_sparse_info.argtypes = [vp, P(i32), P(i32), P(i32), P(C.c_int64), P(C.c_int64)]
     lib.sba_explicit_tiles.argtypes = [vp, vp, vp, vp, vp]
     lib.sba_evaluate_offset.argtypes = [vp, vp, vp, vp, vp, vp]
+    lib.sba_set_intrinsics_blocks.argtypes = [vp, i32, vp, vp]
+    lib.sba_add_intrinsics_priors.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.sba_set_sensor_offsets.argtypes = [vp, vp]
+    lib.sba_set_lever_arms.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.sba_shared_info.argtypes = [vp, P(i32), P(i32), vp, vp]
     lib.sba_bal_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.sba_bal_close.argtypes = [vp]
     lib.sba_bal_close.restype = None

@@ -58,6 +58,17 @@ const char* sba_create_error(void) { return g_create_error.c_str(); }
 
 int sba_set_options(sba_solver* s, const sba_options* o) { GUARD(s && o); const int dev = s->impl.opt.device; s->impl.opt = *o; s->impl.opt.device = dev; return SBA_OK; }
 int sba_set_intrinsics(sba_solver* s, int32_t n, const double* intr10) { GUARD(s); return s->impl.set_intrinsics(n, intr10); }
+int sba_set_intrinsics_blocks(sba_solver* s, int32_t n, double* intr10, const uint8_t* fixed_mask) { GUARD(s); return s->impl.set_intrinsics_blocks(n, intr10, fixed_mask); }
+int sba_add_intrinsics_priors(sba_solver* s, int32_t n, const int32_t* model, const int32_t* block, const double* A9, const double* b3) {
+    GUARD(s); return s->impl.add_intrinsics_priors(n, model, block, A9, b3);
+}
+int sba_set_sensor_offsets(sba_solver* s, const double* offset6) { GUARD(s); return s->impl.set_sensor_offsets(offset6); }
+int sba_set_lever_arms(sba_solver* s, int32_t n_mounts, double* boresight, double* lever, const uint8_t* fixed, const int32_t* cam_mount) {
+    GUARD(s); return s->impl.set_lever_arms(n_mounts, boresight, lever, fixed, cam_mount);
+}
+int sba_shared_info(const sba_solver* s, int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block) {
+    GUARD(s); return s->impl.shared_info(n_ext, n_groups, model_block, mount_block);
+}
 int sba_set_poses(sba_solver* s, double* raxis, double* t, int32_t n, const int32_t* cam_model, const uint8_t* fixed,
                   const uint8_t* cost_kind) { GUARD(s); return s->impl.set_poses(raxis, t, n, cam_model, fixed, cost_kind); }
 int sba_set_points(sba_solver* s, double* xyz, int32_t n, const uint8_t* fixed) { GUARD(s); return s->impl.set_points(xyz, n, fixed); }
@@ -154,7 +165,7 @@ int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* t
     if (tiles && cudaMemcpy(tiles, P.ex_S, n * 384 * 384 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
     if (tile_i && cudaMemcpy(tile_i, P.ex_tile_I, n * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
     if (tile_j && cudaMemcpy(tile_j, P.ex_tile_J, n * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
-    if (rhs && cudaMemcpy(rhs, P.rhs, 6 * (size_t)P.Nc * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
+    if (rhs && cudaMemcpy(rhs, P.rhs, 6 * (size_t)P.Nce * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;
     return SBA_OK;
 }
 

@@ -12,6 +12,7 @@ constexpr int WARPS_PER_BLOCK = 8;   // tile kernels: 256 threads
 constexpr int RED_BLOCK = 1024;      // single-block deterministic reductions
 constexpr int HP = 12;               // doubles per heavy-window partial
 constexpr int TP = 28;               // doubles per tile partial
+constexpr int SBA_MAX_GROUPS = 12;   // free camera models + free mountings of one problem (shared blocks, sba_kernels_shared.cu)
 
 // All arrays are device pointers.  "slot" = position in the camera-sorted,
 // 32-aligned observation order (padding slots have obs_pt = -1 and all-zero J).
@@ -158,6 +159,41 @@ struct DevProblem {
     double* prior_res;    // 3*Nprior
     int32_t Nlonely;      // free points that carry priors but no observation (a ground-control landmark no image sees): they head
     int32_t* lonely_pt;   //   no q slot, so the back-substitution handles them in a list kernel (dp = -Hinv gp)
+    // ---- shared parameter blocks: free intrinsic blocks per camera model and free boresight / lever-arm
+    // blocks per mounting.  They enter the reduced camera system as PSEUDO-CAMERAS (6 columns each) behind the real ones:
+    // extended cameras 0 .. Nce-1, every per-camera array below is allocated for Nce entries, and the tile / PCG kernels are
+    // launched on a copy of this struct with Nc = Nce.  A GROUP = one free model (8 columns f ppx ppy k1 k2 k3 | t1 t2, two
+    // pseudo-cameras, the second one with four dead columns) or one free mounting (6 columns b | l, one pseudo-camera);
+    // internally every group carries 8 columns.  See sba_kernels_shared.cu.
+    int32_t Nce;          // extended cameras (= Nc without shared blocks)
+    int32_t Ng;           // groups
+    int32_t Nmt;          // mountings
+    int32_t grp_kind[SBA_MAX_GROUPS];    // 0 camera model, 1 mounting          } small tables carried in the struct itself
+    int32_t grp_index[SBA_MAX_GROUPS];   // model / mounting                    } (kernel parameter space), also read by
+    int32_t grp_blk[SBA_MAX_GROUPS];     // first pseudo-camera of the group    } the launch wrappers on the host
+    uint8_t grp_live[8 * SBA_MAX_GROUPS];   // column is free (constant blocks and padding are dead: unit diagonal, zero rhs)
+    int32_t* cam_grp;     // 2*Nc: group of the camera's model, of its mounting (-1: none / constant)
+    int32_t* cam_mount;   // Nc: mounting of the camera or -1 (nullptr: no mountings)
+    double* cam_off;      // 12*Nc: constant sensor -> body transform per camera, Roff^T row-major + toff (nullptr: identity)
+    double* mount;        // 6*Nmt: boresight b (axis-angle) | lever arm l
+    double* mount_cache;  // 24*Nmt: pose_cache(b, l)
+    double* mount_saved;  // 6*Nmt
+    double* intr_saved;   // 10*Nm
+    double* sh_W;         // [Ng][Np][24]: W = sum_o A_o^T G_o (3 x 8 row-major), G = d res / d group columns
+    double* sh_Y;         // [Ng][Np][24]: (Hpp + D)^-1 W
+    double* sh_heavy;     // 24 per heavy window (points with more than 32 observations)
+    double* sh_H;         // [Ng][Ng][64]: sum_o G_g^T G_g' (undamped; + priors on the diagonal groups)  } all-reduced
+    double* sh_g;         // [Ng][8]: sum_o G_g^T res (+ priors)                                           } together
+    double* sh_acc;       // per LM iteration, all-reduced: border [Ng][Nc][48] | SS [Ng][Ng][64] = sum_p W_g^T Y_g' | rS [Ng][8] = sum_p W_g^T Hinv gp
+    double* sh_gd;        // 2 planes of Ns: G_o delta of the current step (model cost change)
+    double* sh_part;      // per-block partials of the group reductions (72 doubles per block)
+    int32_t sh_nblk;      // blocks of the persistent point-reduction kernels
+    int32_t Nipr;         // priors on intrinsic blocks (FixedSizeNormalPrior<n,n>, pinholecameraprojectormodule.cpp:327-345 ...)
+    int32_t* ipr_model;   // Nipr
+    int32_t* ipr_block;   // Nipr: 0 f, 1 pp, 2 k, 3 t, 4 B
+    double* ipr_A;        // 9*Nipr: dim x dim row-major in the leading entries
+    double* ipr_b;        // 3*Nipr
+    double* ipr_res;      // 3*Nipr
     // normal-equation blocks
     double* Hpp;          // 8*Np AoS: packed symmetric 3x3 (6) + pad, undamped
     double* gp;           // 4*Np AoS
@@ -267,5 +303,16 @@ void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t s
 void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);
+// shared parameter blocks (sba_kernels_shared.cu)
+int shared_reduce_blocks();                                               // blocks of the persistent point-reduction kernels
+void launch_shared_linearize(const DevProblem& P, cudaStream_t st);       // per linearisation: W per group, sh_H / sh_g partial sums (this rank)
+void launch_shared_lin_finish(const DevProblem& P, cudaStream_t st);      // priors into sh_H / sh_g, Hcc / gc of the pseudo-cameras
+void launch_shared_build(const DevProblem& P, cudaStream_t st);           // per LM iteration: Y = Hinv W, border / SS / rS partial sums into sh_acc
+void launch_shared_build_finish(const DevProblem& P, int write_tiles, cudaStream_t st);   // Sd, rhs of the pseudo-cameras; border / cross blocks into the tiles
+void launch_shared_backsub(const DevProblem& P, const double* x, cudaStream_t st);        // dp -= sum_g Y_g delta_g; G_o delta planes (sh_gd)
+void launch_shared_stats(const DevProblem& P, const double* x, cudaStream_t st);          // step / parameter norms and prior model change of the shared blocks (adds to the replicated scalars)
+void launch_shared_apply(const DevProblem& P, const double* x, cudaStream_t st);          // save + update intrinsics / mountings
+void launch_shared_restore(const DevProblem& P, cudaStream_t st);
+void launch_shared_prior_eval(const DevProblem& P, int store, cudaStream_t st);           // intrinsics priors: residuals (stored if store), cost added to SC_COST_PRIOR_CAM
 
 }  // namespace sba

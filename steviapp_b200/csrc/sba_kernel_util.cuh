@@ -111,7 +111,7 @@ __device__ __forceinline__ void st256(double* p, double a, double b, double c, d
 //   C = W Pi [Pbar]x Jr = A [d]x Q^T,   row k:  C_k = (A_k x d) Q^T
 // for ANY stiffness W, so the passes that need C rebuild it from the A planes, the Pbar planes (Pc) and two per-camera
 // 3x3 constants: 24 B/obs read instead of 48, and K1 writes 48 B/obs less.
-struct CamRQ { double Rt[9], Q[9]; };
+struct CamRQ { double Rt[9], Q[9], dt[3]; };   // Rt of the SENSOR pose, Q of the body pose, dt = ts - t (zero without offsets / mountings)
 __device__ __forceinline__ CamRQ load_cam_rq(const DevProblem& P, int cam) {
     CamRQ c;
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
@@ -120,13 +120,14 @@ __device__ __forceinline__ CamRQ load_cam_rq(const DevProblem& P, int cam) {
     const double* q = P.cam_Q + 12 * (size_t)cam;
     const d4 q0 = ld256(q), q1 = ld256(q + 4), q2 = ld256(q + 8);
     c.Q[0] = q0.x; c.Q[1] = q0.y; c.Q[2] = q0.z; c.Q[3] = q0.w; c.Q[4] = q1.x; c.Q[5] = q1.y; c.Q[6] = q1.z; c.Q[7] = q1.w; c.Q[8] = q2.x;
+    c.dt[0] = q2.y; c.dt[1] = q2.z; c.dt[2] = q2.w;
     return c;
 }
 // A: rows (A[0..2]), (A[3..5]); Pb = Pbar of the slot; C out in the same layout
 __device__ __forceinline__ void rebuild_C(const double* A, double p0, double p1, double p2, const CamRQ& c, double* C) {
-    const double d0 = c.Rt[0] * p0 + c.Rt[3] * p1 + c.Rt[6] * p2;   // d = R Pbar, R = Rt^T
-    const double d1 = c.Rt[1] * p0 + c.Rt[4] * p1 + c.Rt[7] * p2;
-    const double d2 = c.Rt[2] * p0 + c.Rt[5] * p1 + c.Rt[8] * p2;
+    const double d0 = c.Rt[0] * p0 + c.Rt[3] * p1 + c.Rt[6] * p2 + c.dt[0];   // d = X - t = Rs Pbar + (ts - t), Rs = Rt^T
+    const double d1 = c.Rt[1] * p0 + c.Rt[4] * p1 + c.Rt[7] * p2 + c.dt[1];
+    const double d2 = c.Rt[2] * p0 + c.Rt[5] * p1 + c.Rt[8] * p2 + c.dt[2];
 #pragma unroll
     for (int r = 0; r < 2; r++) {
         const double a0 = A[3 * r], a1 = A[3 * r + 1], a2 = A[3 * r + 2];
@@ -139,10 +140,11 @@ __device__ __forceinline__ void rebuild_C(const double* A, double p0, double p1,
 // Cheaper form for the passes that SUM over the observations of one camera: C_k = w_k Q^T with w_k = A_k x d, and Q is a
 // per-camera constant, so they accumulate with the "pre-Q" rows J' = [w | -A] (21 FMA per observation instead of 39) and
 // apply T = diag(Q, I) once per camera:  sum Jc^T M Jc = T (sum J'^T M J') T^T,  sum Jc^T r = T sum J'^T r.
+// Rt = 12 doubles: Rt (9) of the sensor pose followed by dt = ts - t (load_rt)
 __device__ __forceinline__ void preq_rows(const double* A, double p0, double p1, double p2, const double* Rt, double* w) {
-    const double d0 = Rt[0] * p0 + Rt[3] * p1 + Rt[6] * p2;   // d = R Pbar, R = Rt^T
-    const double d1 = Rt[1] * p0 + Rt[4] * p1 + Rt[7] * p2;
-    const double d2 = Rt[2] * p0 + Rt[5] * p1 + Rt[8] * p2;
+    const double d0 = Rt[0] * p0 + Rt[3] * p1 + Rt[6] * p2 + Rt[9];   // d = X - t = Rs Pbar + (ts - t), Rs = Rt^T
+    const double d1 = Rt[1] * p0 + Rt[4] * p1 + Rt[7] * p2 + Rt[10];
+    const double d2 = Rt[2] * p0 + Rt[5] * p1 + Rt[8] * p2 + Rt[11];
 #pragma unroll
     for (int r = 0; r < 2; r++) {
         const double a0 = A[3 * r], a1 = A[3 * r + 1], a2 = A[3 * r + 2];
@@ -153,6 +155,8 @@ __device__ __forceinline__ void load_rt(const DevProblem& P, int cam, double* Rt
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
     const d4 a0 = ld256(cc), a1 = ld256(cc + 4), a2 = ld256(cc + 8);
     Rt[0] = a0.x; Rt[1] = a0.y; Rt[2] = a0.z; Rt[3] = a0.w; Rt[4] = a1.x; Rt[5] = a1.y; Rt[6] = a1.z; Rt[7] = a1.w; Rt[8] = a2.x;
+    const d4 q2 = ld256(P.cam_Q + 12 * (size_t)cam + 8);   // (Q8, dt0, dt1, dt2)
+    Rt[9] = q2.y; Rt[10] = q2.z; Rt[11] = q2.w;
 }
 // in place: packed symmetric 6x6 H' (21, row-major upper) -> T H' T^T, and g' (6) -> T g' (either may be null), T = diag(Q, I)
 __device__ __forceinline__ void preq_finish(const double* Q, double* H21, double* g6) {
@@ -192,15 +196,12 @@ __device__ __forceinline__ void preq_finish(const double* Q, double* H21, double
 constexpr int CAM_VEC_STRIDE = 8;
 __device__ __forceinline__ void cam_vec_store(const DevProblem& P, int c, const double* x6) {
     const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * c;
-    const double* Jr = cc + 12;
-    const double w0 = Jr[0] * x6[0] + Jr[1] * x6[1] + Jr[2] * x6[2];
-    const double w1 = Jr[3] * x6[0] + Jr[4] * x6[1] + Jr[5] * x6[2];
-    const double w2 = Jr[6] * x6[0] + Jr[7] * x6[1] + Jr[8] * x6[2];
-    // R = (Rt)^T
-    const double a0 = cc[0] * w0 + cc[3] * w1 + cc[6] * w2;
-    const double a1 = cc[1] * w0 + cc[4] * w1 + cc[7] * w2;
-    const double a2 = cc[2] * w0 + cc[5] * w1 + cc[8] * w2;
-    const double t0 = cc[9] - P.center[0], t1 = cc[10] - P.center[1], t2 = cc[11] - P.center[2];
+    const double* Q = P.cam_Q + 12 * (size_t)c;   // Q = (R Jr)^T of the BODY pose, Q[9..11] = ts - t
+    // a = R Jr x_r = Q^T x_r
+    const double a0 = Q[0] * x6[0] + Q[3] * x6[1] + Q[6] * x6[2];
+    const double a1 = Q[1] * x6[0] + Q[4] * x6[1] + Q[7] * x6[2];
+    const double a2 = Q[2] * x6[0] + Q[5] * x6[1] + Q[8] * x6[2];
+    const double t0 = cc[9] - Q[9] - P.center[0], t1 = cc[10] - Q[10] - P.center[1], t2 = cc[11] - Q[11] - P.center[2];   // body t - c0
     double* o = P.cam_vec + (size_t)CAM_VEC_STRIDE * c;
     st2(o, a0, a1);
     st2(o + 2, a2, x6[3] + (t1 * a2 - t2 * a1));

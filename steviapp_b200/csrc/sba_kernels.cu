@@ -17,23 +17,73 @@ namespace sba {
 // ---------------------------------------------------------------------------
 // K0 pose cache: thread per camera
 // ---------------------------------------------------------------------------
+__global__ void k_mount_cache(DevProblem P) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= P.Nmt) return;
+    double out[CAM_CACHE_STRIDE];
+    pose_cache(P.mount + 6 * (size_t)k, P.mount + 6 * (size_t)k + 3, out);
+#pragma unroll
+    for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.mount_cache[(size_t)CAM_CACHE_STRIDE * k + i] = out[i];
+}
+// With a constant sensor offset (Roff, toff) and / or a mounting (boresight b, lever arm l) the record holds the SENSOR pose
+//   Rs = R Roff Rb,  ts = t + R (toff + Roff l)        (sensor2world = (pose * offset) * (b, l),
+//   costfunctors/posedecoratorfunctors.h:208,628-700; sbamodules/pinholecameraprojectormodule.cpp:147-214)
+// so that Pbar = Rs^T (X - ts) and A = Pi Rs^T = d res / d X = -d res / d t hold as without them; Jr stays the BODY one and
+// cam_Q = (R Jr)^T | ts - t, because d res / d rAxis = A [X - t]x (R Jr) with the body pose: the readers add ts - t to Rs Pbar.
 __global__ void k_pose_cache(DevProblem P) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= P.Nc) return;
     double out[CAM_CACHE_STRIDE];
     pose_cache(P.cam_r + 3 * c, P.cam_t + 3 * c, out);
     out[21] = P.intr[10 * P.cam_model[c]];   // f of the camera's model: d_z of the plane cost (factored camera pass)
-#pragma unroll
-    for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
     // Q = (R Jr)^T: C = A [X - t]x Q^T (explicit reduced system, sba_kernels_explicit.cu).  R[i][k] = Rt[3k+i]
     double* Q = P.cam_Q + 12 * (size_t)c;
 #pragma unroll
     for (int r = 0; r < 3; r++)
 #pragma unroll
         for (int a = 0; a < 3; a++) Q[3 * r + a] = out[a] * out[12 + r] + out[3 + a] * out[15 + r] + out[6 + a] * out[18 + r];
-    Q[9] = Q[10] = Q[11] = 0.0;
+    double dt[3] = {0.0, 0.0, 0.0};
+    const int mt = P.cam_mount ? P.cam_mount[c] : -1;
+    if (P.cam_off || mt >= 0) {
+        double M[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, cb[3] = {0, 0, 0};   // M = sensor <- body rotation (Rb^T Roff^T), cb = sensor origin in the body frame
+        if (P.cam_off) {
+            const double* off = P.cam_off + 12 * (size_t)c;
+#pragma unroll
+            for (int i = 0; i < 9; i++) M[i] = off[i];
+            cb[0] = off[9]; cb[1] = off[10]; cb[2] = off[11];
+        }
+        if (mt >= 0) {
+            const double* cl = P.mount_cache + (size_t)CAM_CACHE_STRIDE * mt;   // Rb^T, l
+            // cb += Roff l = M_off^T l ; M = Rb^T M_off
+            double c2[3], M2[9];
+#pragma unroll
+            for (int i = 0; i < 3; i++) c2[i] = cb[i] + M[i] * cl[9] + M[3 + i] * cl[10] + M[6 + i] * cl[11];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int j = 0; j < 3; j++) M2[3 * i + j] = cl[3 * i] * M[j] + cl[3 * i + 1] * M[3 + j] + cl[3 * i + 2] * M[6 + j];
+#pragma unroll
+            for (int i = 0; i < 9; i++) M[i] = M2[i];
+            cb[0] = c2[0]; cb[1] = c2[1]; cb[2] = c2[2];
+        }
+        // dt = R cb (R = Rt^T), Rs^T = M Rt
+#pragma unroll
+        for (int i = 0; i < 3; i++) dt[i] = out[i] * cb[0] + out[3 + i] * cb[1] + out[6 + i] * cb[2];
+        double Rs[9];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) Rs[3 * i + j] = M[3 * i] * out[j] + M[3 * i + 1] * out[3 + j] + M[3 * i + 2] * out[6 + j];
+#pragma unroll
+        for (int i = 0; i < 9; i++) out[i] = Rs[i];
+        out[9] += dt[0]; out[10] += dt[1]; out[11] += dt[2];
+    }
+    Q[9] = dt[0]; Q[10] = dt[1]; Q[11] = dt[2];
+#pragma unroll
+    for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
 }
 void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
+    if (P.Nmt) k_mount_cache<<<cdiv(P.Nmt, 128), 128, 0, st>>>(P);
     k_pose_cache<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);
 }
 

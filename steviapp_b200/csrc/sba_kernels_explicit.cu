@@ -81,8 +81,12 @@ __global__ void __launch_bounds__(128) k_explicit_assemble(DevProblem P) {
     if (b >= P.ex_nblocks) return;
     const int i = __ldg(P.ex_blk_i + b), j = __ldg(P.ex_blk_j + b);
     const int r0 = __ldg(P.ex_blk_off + b), r1 = r0 + __ldg(P.ex_blk_len + b);
-    const d4 ti = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * i + 8);   // (Rt8, t0, t1, t2)
-    const d4 tj = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * j + 8);
+    d4 ti = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * i + 8);   // (Rt8, t0, t1, t2) of the sensor pose
+    d4 tj = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * j + 8);
+    {   // body t = ts - (ts - t): the second term sits behind Q (zero without offsets / mountings)
+        const d4 qi = ld256(P.cam_Q + 12 * (size_t)i + 8), qj = ld256(P.cam_Q + 12 * (size_t)j + 8);
+        ti.y -= qi.y; ti.z -= qi.z; ti.w -= qi.w; tj.y -= qj.y; tj.z -= qj.z; tj.w -= qj.w;
+    }
     double B[36];
 #pragma unroll
     for (int e = 0; e < 36; e++) B[e] = 0.0;

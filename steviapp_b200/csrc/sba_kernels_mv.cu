@@ -104,12 +104,22 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, CPF_BATCH >= 4 ? 3 : (CP
     for (int i = 0; i < 3; i++) { S1[i] = warp_sum(S1[i]); S2[i] = warp_sum(S2[i]); }
     if (lane == 0) {
         double* out = P.mv_part + 6 * (size_t)tile;
-        const double* Jr = cc + 12;
-        // C^T b summed = -Jr^T S1 ; -A^T b summed = -R S2 = -(Rt)^T S2
+        // with Rs = Rt^T (sensor pose), Q = (R Jr)^T (body pose) and dt = ts - t:
+        //   C^T b summed = -Q (Rs S1 + dt x (Rs S2)) ;  -A^T b summed = -Rs S2
+        // (without offsets / mountings dt = 0 and Q Rs = Jr^T: the form -Jr^T S1 of the plain projector)
+        const double* Q = P.cam_Q + 12 * (size_t)cam;
+        double u[3], v[3];
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            out[a] = -(__ldg(Jr + a) * S1[0] + __ldg(Jr + 3 + a) * S1[1] + __ldg(Jr + 6 + a) * S1[2]);
-            out[3 + a] = -(Rt[a] * S2[0] + Rt[3 + a] * S2[1] + Rt[6 + a] * S2[2]);
+            u[a] = Rt[a] * S1[0] + Rt[3 + a] * S1[1] + Rt[6 + a] * S1[2];
+            v[a] = Rt[a] * S2[0] + Rt[3 + a] * S2[1] + Rt[6 + a] * S2[2];
+        }
+        const double d0 = __ldg(Q + 9), d1 = __ldg(Q + 10), d2 = __ldg(Q + 11);
+        u[0] += d1 * v[2] - d2 * v[1]; u[1] += d2 * v[0] - d0 * v[2]; u[2] += d0 * v[1] - d1 * v[0];
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            out[a] = -(__ldg(Q + 3 * a) * u[0] + __ldg(Q + 3 * a + 1) * u[1] + __ldg(Q + 3 * a + 2) * u[2]);
+            out[3 + a] = -v[a];
         }
     }
 }

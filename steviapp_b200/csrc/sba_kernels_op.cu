@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_schur_diag(DevProblem 
     if (tile >= P.Nt) return;
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
-    double Rt[9];
+    double Rt[12];
     load_rt(P, __ldg(P.tile_cam + tile), Rt);
     double D[21];
 #pragma unroll

@@ -330,6 +330,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
         const double v[3] = {d1 * ac2 - d2 * ac1 - gc0 + d01.x, d2 * ac0 - d0 * ac2 - gc1 + d01.y, d0 * ac1 - d1 * ac0 - gc2 + d23.x};
 #pragma unroll
         for (int a = 0; a < 3; a++) { m0 += A[a] * v[a]; m1 += A[3 + a] * v[a]; }
+        if (P.sh_gd) { m0 += __ldcs(P.sh_gd + s); m1 += __ldcs(P.sh_gd + Ns + s); }   // + G_o delta of the shared blocks (sba_kernels_shared.cu)
         const double e0 = __ldcs(P.res + s), e1 = __ldcs(P.res + Ns + s);
         acc += m0 * (e0 + 0.5 * m0) + m1 * (e1 + 0.5 * m1);
     }

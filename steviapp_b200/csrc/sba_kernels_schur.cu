@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProbl
     if (tile >= P.Nt) return;
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
-    double Rt[9];
+    double Rt[12];
     load_rt(P, __ldg(P.tile_cam + tile), Rt);
     double H[21], g[6];
 #pragma unroll

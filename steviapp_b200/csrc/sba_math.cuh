@@ -320,8 +320,18 @@ SBA_HD bool obs_eval_leverarm(const double* cc, const double* off, const double*
 //   res = W e(Pbar, d),  d = dirFromUV(uv; intr)  ->  d res / d intr = W (d e / d d) (d d / d intr);
 // the B columns are identically zero (the skew is built from the tangential block, pinholecameraprojectormodule.h:46-47).
 // Returns false (and zeros) when the plane cost fails (Pbar.z < 0).
+SBA_HD bool obs_intr_jac_pbar(double Px, double Py, double Pz, double u, double v, const double* in, const double* W,
+                              int spherical, double* J);
 SBA_HD bool obs_intr_jac(const double* cc, const double* X, double u, double v, const double* in, const double* W,
                          int spherical, double* J) {
+    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
+    return obs_intr_jac_pbar(cc[0] * vx + cc[1] * vy + cc[2] * vz, cc[3] * vx + cc[4] * vy + cc[5] * vz,
+                             cc[6] * vx + cc[7] * vy + cc[8] * vz, u, v, in, W, spherical, J);
+}
+// same from the sensor-frame point Pbar (what the camera-order planes hold; with a sensor offset / lever arm Pbar is the point in
+// the SENSOR frame, so this form serves every projector variant)
+SBA_HD bool obs_intr_jac_pbar(double Px, double Py, double Pz, double u, double v, const double* in, const double* W,
+                              int spherical, double* J) {
     for (int k = 0; k < 20; k++) J[k] = 0.0;
     // ---- d and d d / d intr (3 x 8; d_z = f)
     const double f = in[0], t1 = in[6], t2 = in[7];
@@ -350,10 +360,6 @@ SBA_HD bool obs_intr_jac(const double* cc, const double* X, double u, double v, 
     dd0[7] = f * (r2 + 2.0 * x * x + g0x * x_t2);      dd1[7] = f * (2.0 * xy + g1x * x_t2);
     const double d0 = g0 * f, d1 = g1 * f, d2 = f;
     // ---- d e / d d (2 x 3): rows (ex0, 0, ex2), (0, ey1, ey2)
-    const double vx = X[0] - cc[9], vy = X[1] - cc[10], vz = X[2] - cc[11];
-    const double Px = cc[0] * vx + cc[1] * vy + cc[2] * vz;
-    const double Py = cc[3] * vx + cc[4] * vy + cc[5] * vz;
-    const double Pz = cc[6] * vx + cc[7] * vy + cc[8] * vz;
     double ex0, ex2, ey1, ey2;
     if (!spherical) {
         if (Pz < 0.0) return false;
@@ -379,6 +385,40 @@ SBA_HD bool obs_intr_jac(const double* cc, const double* X, double u, double v, 
     return true;
 }
 
+
+// d res / d (boresight b[3], leverArm l[3]) of one observation behind a free mounting (LeverArm<UVCost,
+// Body2World | Sensor2Body>, costfunctors/posedecoratorfunctors.h:148-264), 2 x 6 row-major, from the SENSOR-frame point
+// Pbar = Rb^T (m - l): with G = Pi Rb^T,  d e / d l = -G,  d e / d b = Pi [Pbar]x Jr(b).  cl = pose_cache(b, l).
+// Returns false (and zeros) when the plane cost fails.
+SBA_HD bool obs_lever_jac_pbar(double Px, double Py, double Pz, const double* d, const double* cl, const double* W,
+                               int spherical, double* J) {
+    for (int k = 0; k < 12; k++) J[k] = 0.0;
+    double p00, p02, p11, p12;
+    if (!spherical) {
+        if (Pz < 0.0) return false;
+        const double iz = 1.0 / Pz, s = d[2] * iz;
+        p00 = s; p11 = s; p02 = -s * (Px * iz); p12 = -s * (Py * iz);
+    } else {
+        const double kx = (d[0] * d[0] + d[2] * d[2]) / d[2], ky = (d[1] * d[1] + d[2] * d[2]) / d[2];
+        const double qx = kx / (Px * Px + Pz * Pz), qy = ky / (Py * Py + Pz * Pz);
+        p00 = qx * Pz; p02 = -qx * Px; p11 = qy * Pz; p12 = -qy * Py;
+    }
+    double E[12];
+    const double pi0[3] = {p00, 0.0, p02}, pi1[3] = {0.0, p11, p12};
+    for (int k = 0; k < 2; k++) {
+        const double* pi = k ? pi1 : pi0;
+        const double s0 = pi[1] * Pz - pi[2] * Py, s1 = -pi[0] * Pz + pi[2] * Px, s2 = pi[0] * Py - pi[1] * Px;   // pi [Pbar]x
+        for (int j = 0; j < 3; j++) {
+            E[6 * k + j] = s0 * cl[12 + j] + s1 * cl[15 + j] + s2 * cl[18 + j];                     // ... Jr(b)
+            E[6 * k + 3 + j] = -(pi[0] * cl[j] + pi[1] * cl[3 + j] + pi[2] * cl[6 + j]);          // -Pi Rb^T
+        }
+    }
+    for (int c = 0; c < 6; c++) {
+        J[c] = W ? W[0] * E[c] + W[1] * E[6 + c] : E[c];
+        J[6 + c] = W ? W[2] * E[c] + W[3] * E[6 + c] : E[6 + c];
+    }
+    return true;
+}
 
 // Pi = d e / d Pbar rebuilt from Pbar and the aux scale constants (identity stiffness):
 // rows (p00, 0, p02), (0, p11, p12).  Same expressions as in obs_eval.

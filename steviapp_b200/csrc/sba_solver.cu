@@ -168,6 +168,7 @@ int Solver::add_priors(int32_t n, const int32_t* kind, const int32_t* index, con
 
 }  // namespace sba
 
+#include "sba_solver_shared.inc"
 #include "sba_solver_layout.inc"
 #include "sba_solver_explicit.inc"
 #include "sba_solver_lm.inc"

@@ -71,6 +71,12 @@ public:
     int open_device();
 
     int set_intrinsics(int32_t n, const double* intr10);
+    // shared blocks (sba_solver_shared.inc)
+    int set_intrinsics_blocks(int32_t n, double* intr10, const uint8_t* fixed_mask);
+    int add_intrinsics_priors(int32_t n, const int32_t* model, const int32_t* block, const double* A9, const double* b3);
+    int set_sensor_offsets(const double* offset6);
+    int set_lever_arms(int32_t n_mounts, double* boresight, double* lever, const uint8_t* fixed, const int32_t* cam_mount);
+    int shared_info(int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block) const;
     int set_poses(double* raxis, double* t, int32_t n, const int32_t* model, const uint8_t* fixed, const uint8_t* kind);
     int set_points(double* xyz, int32_t n, const uint8_t* fixed);
     int add_observations(int32_t n, const int32_t* cam, const int32_t* pt, const double* uv, const double* info);
@@ -95,6 +101,8 @@ public:
     void* cb_user = nullptr;
     DevProblem P{};
     bool finalized = false;
+    // the tile / PCG / per-camera vector kernels see the pseudo-cameras of the shared blocks as cameras
+    DevProblem Pe() const { DevProblem e = P; e.Nc = P.Nce; return e; }
 
 private:
     int fail(int code, const std::string& msg);
@@ -118,6 +126,19 @@ private:
     std::vector<int32_t> prior_kind, prior_index; std::vector<double> prior_A, prior_b;
     std::vector<int32_t> slot_of_obs;
     int32_t* d_slot_of_obs = nullptr;
+    // shared blocks: caller-owned arrays updated in place like the pose / point blocks
+    double* h_intr_rw = nullptr;                       // n_models * 10 (set_intrinsics_blocks), else nullptr: intrinsics constant
+    std::vector<uint8_t> intr_fixed_mask;              // per model, bit k: block k (f, pp, k, t, B) constant
+    std::vector<int32_t> ipr_model, ipr_block; std::vector<double> ipr_A, ipr_b;
+    std::vector<double> cam_offset6;                   // per camera (r_off, t_off), empty: identity
+    double* h_mount_b = nullptr; double* h_mount_l = nullptr; int32_t Nmt = 0;
+    std::vector<uint8_t> mount_fixed; std::vector<int32_t> cam_mount;
+    int32_t Nce = 0;
+    std::vector<int32_t> model_block, mount_block;     // first pseudo-camera of a free model / mounting, -1: constant
+    int plan_shared_blocks();                          // groups + pseudo-cameras (before the allocations of finalize)
+    int upload_shared_tables();                        // device side of the shared blocks (after the allocations)
+    int shared_linearize();                            // W, sh_H, sh_g (+ all-reduce), Hcc / gc of the pseudo-cameras
+    int shared_build();                                // Y, border, Schur terms (+ all-reduce), Sd / rhs / tile blocks of the pseudo-cameras
 
     DeviceArena arena;
     cudaStream_t st = nullptr;

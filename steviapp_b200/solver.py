@@ -114,6 +114,51 @@ class SBASolver:
         self._keep["intr"] = intr
         self._check(self._lib.sba_set_intrinsics(self._h, intr.shape[0], _ptr(intr)))
 
+    def set_intrinsics_blocks(self, intr, fixed_mask=None):
+        """Camera models whose blocks f, pp, k, t, B may be FREE (the reference's default).  intr: (n_models, 10) float64
+        C-contiguous, UPDATED IN PLACE by solve(); fixed_mask: per model, bit k set -> block k constant (None: all constant)."""
+        if not (isinstance(intr, np.ndarray) and intr.dtype == np.float64 and intr.flags.c_contiguous and intr.flags.writeable):
+            raise TypeError("intr must be a writeable C-contiguous float64 ndarray (it is updated in place)")
+        n = intr.size // 10
+        fm = None if fixed_mask is None else np.ascontiguousarray(fixed_mask, dtype=np.uint8)
+        if fm is not None and fm.size != n:
+            raise ValueError("fixed_mask must have one entry per camera model")
+        self._keep.update(intr=intr, intr_mask=fm)
+        self._check(self._lib.sba_set_intrinsics_blocks(self._h, n, _ptr(intr), _ptr(fm)))
+
+    def add_intrinsics_priors(self, model, block, A, b):
+        """FixedSizeNormalPrior<n,n> on intrinsic blocks: A (n, 9) with dim x dim row-major leading entries, b (n, 3)."""
+        model = np.ascontiguousarray(model, dtype=np.int32); block = np.ascontiguousarray(block, dtype=np.int32)
+        A = _f64(A); b = _f64(b)
+        if block.size != model.size or A.size != 9 * model.size or b.size != 3 * model.size:
+            raise ValueError("intrinsics priors: model/block/A/b sizes disagree")
+        self._check(self._lib.sba_add_intrinsics_priors(self._h, model.size, _ptr(model), _ptr(block), _ptr(A), _ptr(b)))
+
+    def set_sensor_offsets(self, offset6):
+        """Constant sensor -> body transform per camera, (n_cams, 6) = (r_off, t_off); None = identity."""
+        off = None if offset6 is None else _f64(offset6)
+        self._check(self._lib.sba_set_sensor_offsets(self._h, _ptr(off)))
+
+    def set_lever_arms(self, boresight, lever, cam_mount, fixed=None):
+        """Free boresight / lever-arm blocks: boresight, lever (n_mounts, 3) float64, UPDATED IN PLACE; cam_mount (n_cams) int32, -1 = none."""
+        for name, a in (("boresight", boresight), ("lever", lever)):
+            if not (isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.c_contiguous and a.flags.writeable):
+                raise TypeError(f"{name} must be a writeable C-contiguous float64 ndarray (it is updated in place)")
+        n = boresight.size // 3
+        cm = np.ascontiguousarray(cam_mount, dtype=np.int32)
+        fx = None if fixed is None else np.ascontiguousarray(fixed, dtype=np.uint8)
+        self._keep.update(mount_b=boresight, mount_l=lever, cam_mount=cm, mount_fixed=fx)
+        self._check(self._lib.sba_set_lever_arms(self._h, n, _ptr(boresight), _ptr(lever), _ptr(fx), _ptr(cm)))
+
+    def shared_info(self):
+        """Layout of the reduced camera system: extended cameras, groups, first pseudo-camera of every model / mounting (-1: constant)."""
+        n_ext, n_g = C.c_int32(), C.c_int32()
+        nm = self._keep["intr"].size // 10 if "intr" in self._keep else 0
+        nt = self._keep["mount_b"].size // 3 if "mount_b" in self._keep else 0
+        mb = np.full(max(nm, 1), -1, dtype=np.int32); tb = np.full(max(nt, 1), -1, dtype=np.int32)
+        self._check(self._lib.sba_shared_info(self._h, C.byref(n_ext), C.byref(n_g), _ptr(mb), _ptr(tb)))
+        return {"n_ext": n_ext.value, "n_groups": n_g.value, "model_block": mb[:nm], "mount_block": tb[:nt]}
+
     def set_poses(self, raxis, t, cam_model=None, fixed=None, cost_kind=None):
         """raxis, t: (n,3) float64 C-contiguous arrays, sensor->world; UPDATED IN PLACE by solve()."""
         for name, a in (("raxis", raxis), ("t", t)):
@@ -228,7 +273,7 @@ class SBASolver:
         info = self.explicit_info()
         if not info["enabled"]:
             raise SBAError(-1, "explicit reduced camera system is off")
-        nt, nc = info["n_tiles"], self.sizes()["n_cams"]
+        nt, nc = info["n_tiles"], max(self.sizes()["n_cams"], self.shared_info()["n_ext"])
         tiles = np.empty((nt, 384, 384)); ti = np.empty(nt, dtype=np.int32); tj = np.empty(nt, dtype=np.int32)
         rhs = np.empty(6 * nc)
         self._check(self._lib.sba_explicit_tiles(self._h, _ptr(tiles), _ptr(ti), _ptr(tj), _ptr(rhs)))

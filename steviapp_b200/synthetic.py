@@ -213,8 +213,20 @@ def load_into(solver, scene, copy=True):
     raxis = scene["raxis"].copy() if copy else scene["raxis"]
     t = scene["t"].copy() if copy else scene["t"]
     pts = scene["pts"].copy() if copy else scene["pts"]
-    solver.set_intrinsics(scene["intrinsics"])
-    solver.set_poses(raxis, t, scene["cam_model"], scene["cam_fixed"], scene["cost_kind"])
+    if scene.get("intr_fixed_mask") is not None:      # free intrinsic blocks: the array is updated in place (solver.intrinsics)
+        solver.intrinsics = np.ascontiguousarray(scene["intrinsics"], dtype=np.float64).reshape(-1, 10).copy()
+        solver.set_intrinsics_blocks(solver.intrinsics, scene["intr_fixed_mask"])
+        if scene.get("intr_prior_model") is not None:
+            solver.add_intrinsics_priors(scene["intr_prior_model"], scene["intr_prior_block"], scene["intr_prior_A"], scene["intr_prior_b"])
+    else:
+        solver.set_intrinsics(scene["intrinsics"])
+    solver.set_poses(raxis, t, scene["cam_model"], scene["cam_fixed"], scene.get("cost_kind"))
+    if scene.get("cam_offset") is not None:
+        solver.set_sensor_offsets(scene["cam_offset"])
+    if scene.get("mount_b") is not None:
+        solver.mount_b = np.ascontiguousarray(scene["mount_b"], dtype=np.float64).reshape(-1, 3).copy()
+        solver.mount_l = np.ascontiguousarray(scene["mount_l"], dtype=np.float64).reshape(-1, 3).copy()
+        solver.set_lever_arms(solver.mount_b, solver.mount_l, scene["cam_mount"], scene.get("mount_fixed"))
     solver.set_points(pts, scene["pt_fixed"])
     solver.add_observations(scene["obs_cam"], scene["obs_pt"], scene["obs_uv"], scene["obs_info"])
     if scene["prior_kind"].size:
