@@ -348,7 +348,7 @@ def test_block_sparse_panels_match_dense_tiles(case, monkeypatch):
         out[sparse] = s.solve(max_iterations=4, **FIXED_ITERS)
         s.close()
     a, b = out["1"], out["0"]
-    assert all(abs(x - y) <= 1 for x, y in zip(a["pcg_iters_history"], b["pcg_iters_history"]))
+    assert all(abs(x - y) <= 2 for x, y in zip(a["pcg_iters_history"], b["pcg_iters_history"])), (a["pcg_iters_history"], b["pcg_iters_history"])
     for x, y in zip(a["cost_history"], b["cost_history"]):
         assert abs(x - y) <= 1e-10 * max(y, 1.0)
 
