@@ -160,6 +160,24 @@ int sba_set_lever_arms(sba_solver* s, int32_t n_mounts, double* boresight, doubl
  * model_block[m] / mount_block[k] = first pseudo-camera or -1.  Any pointer may be NULL.  Measurement / test hook. */
 int sba_shared_info(const sba_solver* s, int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block);
 
+/* UV <-> UV cross-projection factors: ProjectorModule::addCrossProjectionCostFunction
+ * (modularsbasolver.h / modularsbasolver.cpp:1616-1739) with the plain decorators (identity offsets, no lever arms), i.e. the
+ * functor InvertPoseDynamic<InvertPoseDynamic<UV2UVCost>> (costfunctors/modularuvprojection.h:660-795): factor k links poses
+ * cam1[k], cam2[k] through the pixels uv1, uv2 (2 n each) with stiffness info1, info2 (4 n each, row-major, both NULL =
+ * identity); 4 residuals, no landmark.  The intrinsic blocks of the two cameras' models take part when they are free. */
+int sba_add_uv_pairs(sba_solver* s, int32_t n, const int32_t* cam1, const int32_t* cam2, const double* uv1, const double* uv2,
+                     const double* info1, const double* info2);
+/* loss on those factors: 0 none, 1 ceres::HuberLoss(a), 2 CauchyLoss(a), 3 ArctanLoss(a) -- the reference passes a = 1
+ * (sbamodules/correspondencessetsbamodule.cpp:2459-2471); applied as Ceres' Corrector does (residual / Jacobian rescaling) */
+#define SBA_LOSS_NONE 0
+#define SBA_LOSS_HUBER 1
+#define SBA_LOSS_CAUCHY 2
+#define SBA_LOSS_ARCTAN 3
+int sba_set_pair_loss(sba_solver* s, int32_t kind, double a);
+/* raw residuals (4 per factor) and raw pose Jacobians (4 x 12 row-major: d/d rAxis1, t1, rAxis2, t2) before the loss;
+ * ceres::Problem::Evaluate on those residual blocks.  Parity hook. */
+int sba_evaluate_pairs(sba_solver* s, double* res4, double* jac48);
+
 /* Pose blocks: getNodeForFrame + initManagedParameters
  * (modularsbasolver.cpp:233-306,804-870).  raxis/t are 3*n AoS, caller-owned,
  * updated in place by sba_solve.  fixed -> SetParameterBlockConstant. */

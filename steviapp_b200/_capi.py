@@ -28,6 +28,7 @@ EXPORTS = [
     "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
     "sba_pushbroom_equivalent_uv",
     "sba_set_intrinsics_blocks", "sba_add_intrinsics_priors", "sba_set_sensor_offsets", "sba_set_lever_arms", "sba_shared_info",
+    "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
 ]
 
 
@@ -119,6 +120,9 @@ def load():
     lib.sba_set_sensor_offsets.argtypes = [vp, vp]
     lib.sba_set_lever_arms.argtypes = [vp, i32, vp, vp, vp, vp]
     lib.sba_shared_info.argtypes = [vp, P(i32), P(i32), vp, vp]
+    lib.sba_add_uv_pairs.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.sba_set_pair_loss.argtypes = [vp, i32, dbl]
+    lib.sba_evaluate_pairs.argtypes = [vp, vp, vp]
     lib.sba_bal_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.sba_bal_close.argtypes = [vp]
     lib.sba_bal_close.restype = None

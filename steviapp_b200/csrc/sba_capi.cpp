@@ -66,6 +66,10 @@ int sba_set_sensor_offsets(sba_solver* s, const double* offset6) { GUARD(s); ret
 int sba_set_lever_arms(sba_solver* s, int32_t n_mounts, double* boresight, double* lever, const uint8_t* fixed, const int32_t* cam_mount) {
     GUARD(s); return s->impl.set_lever_arms(n_mounts, boresight, lever, fixed, cam_mount);
 }
+int sba_add_uv_pairs(sba_solver* s, int32_t n, const int32_t* cam1, const int32_t* cam2, const double* uv1, const double* uv2,
+                     const double* info1, const double* info2) { GUARD(s); return s->impl.add_uv_pairs(n, cam1, cam2, uv1, uv2, info1, info2); }
+int sba_set_pair_loss(sba_solver* s, int32_t kind, double a) { GUARD(s); return s->impl.set_pair_loss(kind, a); }
+int sba_evaluate_pairs(sba_solver* s, double* res4, double* jac48) { GUARD(s); return s->impl.evaluate_pairs(res4, jac48); }
 int sba_shared_info(const sba_solver* s, int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block) {
     GUARD(s); return s->impl.shared_info(n_ext, n_groups, model_block, mount_block);
 }

@@ -194,6 +194,24 @@ struct DevProblem {
     double* ipr_A;        // 9*Nipr: dim x dim row-major in the leading entries
     double* ipr_b;        // 3*Nipr
     double* ipr_res;      // 3*Nipr
+    // ---- UV <-> UV cross-projection factors between two poses (sba_kernels_pairs.cu), replicated on every rank ----
+    int32_t Npair;
+    int32_t pair_loss;    // 0 none, 1 Huber, 2 Cauchy, 3 Arctan
+    double pair_loss_a;
+    int32_t* pair_cam;    // 2*Npair
+    double* pair_uv;      // 4*Npair: uv1, uv2
+    double* pair_info;    // 8*Npair: info1, info2 (2x2 row-major) or nullptr
+    double* pair_rho;     // Npair: rho(|r|^2)
+    double* pair_r;       // 4*Npair: corrected residuals
+    double* pair_J;       // 48*Npair: corrected Jacobians 4 x 12 (pose 1 | pose 2), zero at constant cameras
+    double* pair_Ji;      // 64*Npair: 4 x 16, the 8 intrinsic columns of camera 1's model | of camera 2's (nullptr: no free model)
+    double* pair_border;  // [Ng][Nc][48]: sum over a camera's factors of Jc^T Ji (added to the border of the shared blocks)
+    int32_t* pair_inc_off;// Nc+1: incidence list of every camera ...
+    int32_t* pair_inc;    // ... entries 2 * factor + side
+    int32_t Npblk;        // distinct camera pairs (i < j)
+    int32_t* pblk_i; int32_t* pblk_j; int32_t* pblk_off;   // Npblk (+1): factors of the pair ...
+    int32_t* pblk_list;   // ... entries 2 * factor + (1: the factor's SECOND camera is i)
+    uint8_t* pblk_assembled;   // Npblk: the block also receives point contributions (add) or not (assign)
     // normal-equation blocks
     double* Hpp;          // 8*Np AoS: packed symmetric 3x3 (6) + pad, undamped
     double* gp;           // 4*Np AoS
@@ -303,6 +321,12 @@ void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t s
 void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);
+// UV <-> UV factors (sba_kernels_pairs.cu)
+void launch_pair_eval(const DevProblem& P, int store, cudaStream_t st);          // residuals / corrected Jacobians (store) and the cost, added to SC_COST_PRIOR_CAM
+void launch_pair_camera_blocks(const DevProblem& P, cudaStream_t st);           // Hcc, gc (+ sh_H, sh_g, pair_border with free intrinsics)
+void launch_pair_blocks(const DevProblem& P, cudaStream_t st);                  // J_i^T J_j into the tiles (after the assembly)
+void launch_pair_model(const DevProblem& P, const double* x, cudaStream_t st);  // model cost change, added to SC_MODEL_PRIOR_CAM
+void launch_pair_raw(const DevProblem& P, double* res, double* jac, cudaStream_t st);   // inspection hook
 // shared parameter blocks (sba_kernels_shared.cu)
 int shared_reduce_blocks();                                               // blocks of the persistent point-reduction kernels
 void launch_shared_linearize(const DevProblem& P, cudaStream_t st);       // per linearisation: W per group, sh_H / sh_g partial sums (this rank)

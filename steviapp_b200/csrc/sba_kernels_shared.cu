@@ -452,8 +452,9 @@ __global__ void k_shared_border_reduce(DevProblem P, int g, const double* __rest
         v[0] = Q[0] * v0 + Q[1] * v1 + Q[2] * v2; v[1] = Q[3] * v0 + Q[4] * v1 + Q[5] * v2; v[2] = Q[6] * v0 + Q[7] * v1 + Q[8] * v2;
     }
     double* out = P.sh_acc + ((size_t)g * P.Nc + cam) * 48;
+    const double* pb = P.pair_border ? P.pair_border + ((size_t)g * P.Nc + cam) * 48 : nullptr;   // UV <-> UV factors: + Jc^T Ji (replicated: rank 0 only, see launch)
 #pragma unroll
-    for (int a = 0; a < 6; a++) out[8 * a + c] = v[a];
+    for (int a = 0; a < 6; a++) out[8 * a + c] = v[a] + (pb ? pb[8 * a + c] : 0.0);
 }
 int shared_reduce_blocks() {
     static int n = 0;

@@ -96,6 +96,36 @@ SBA_HD void dir_from_uv(double u, double v, const double* in, double* d) {
     d[2] = f;
 }
 
+// dirFromUV and its Jacobian with respect to (f, ppx, ppy, k1, k2, k3, t1, t2): dd[8 r + c] = d d_r / d intr_c, r = x, y, z
+// (d_z = f).  Same expressions as in obs_intr_jac_pbar below.
+SBA_HD void dir_from_uv_jac(double u, double v, const double* in, double* d, double* dd) {
+    const double f = in[0], t1 = in[6], t2 = in[7];
+    const double y = (v - in[2]) / f;
+    const double D = f + t1;
+    const double x = (u - in[1] - t2 * y) / D;
+    const double r2 = x * x + y * y;
+    const double rad = r2 * (in[3] + r2 * (in[4] + r2 * in[5]));
+    const double Rp = in[3] + r2 * (2.0 * in[4] + 3.0 * r2 * in[5]);
+    const double xy = x * y;
+    const double g0 = x + x * rad + 2.0 * xy * t1 + (r2 + 2.0 * x * x) * t2;
+    const double g1 = y + y * rad + (r2 + 2.0 * y * y) * t1 + 2.0 * xy * t2;
+    const double g0x = 1.0 + rad + 2.0 * x * x * Rp + 2.0 * y * t1 + 6.0 * x * t2, g0y = 2.0 * xy * Rp + 2.0 * x * t1 + 2.0 * y * t2;
+    const double g1x = g0y, g1y = 1.0 + rad + 2.0 * y * y * Rp + 6.0 * y * t1 + 2.0 * x * t2;
+    const double y_f = -y / f, y_py = -1.0 / f;
+    const double x_f = (t2 * y / f - x) / D, x_px = -1.0 / D, x_py = t2 / (f * D), x_t1 = -x / D, x_t2 = -y / D;
+    d[0] = g0 * f; d[1] = g1 * f; d[2] = f;
+    dd[0] = g0 + f * (g0x * x_f + g0y * y_f); dd[8] = g1 + f * (g1x * x_f + g1y * y_f);
+    dd[1] = f * g0x * x_px;                   dd[9] = f * g1x * x_px;
+    dd[2] = f * (g0x * x_py + g0y * y_py);    dd[10] = f * (g1x * x_py + g1y * y_py);
+    dd[3] = f * x * r2;                       dd[11] = f * y * r2;
+    dd[4] = f * x * r2 * r2;                  dd[12] = f * y * r2 * r2;
+    dd[5] = f * x * r2 * r2 * r2;             dd[13] = f * y * r2 * r2 * r2;
+    dd[6] = f * (2.0 * xy + g0x * x_t1);            dd[14] = f * (r2 + 2.0 * y * y + g1x * x_t1);
+    dd[7] = f * (r2 + 2.0 * x * x + g0x * x_t2);    dd[15] = f * (2.0 * xy + g1x * x_t2);
+    dd[16] = 1.0;
+    for (int c = 1; c < 8; c++) dd[16 + c] = 0.0;
+}
+
 // One observation.  cc = camera cache record, X = point, d = view ray,
 // W = 2x2 stiffness (row-major) or nullptr (identity).
 // Outputs: res[2]; if JAC: Jc[12] = rows [d/dr(3) d/dt(3)], Jp[6] = rows d/dX(3).

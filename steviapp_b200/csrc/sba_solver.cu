@@ -173,3 +173,4 @@ int Solver::add_priors(int32_t n, const int32_t* kind, const int32_t* index, con
 #include "sba_solver_explicit.inc"
 #include "sba_solver_lm.inc"
 #include "sba_solver_hooks.inc"
+#include "sba_solver_pairs.inc"

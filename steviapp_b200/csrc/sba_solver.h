@@ -77,6 +77,10 @@ public:
     int set_sensor_offsets(const double* offset6);
     int set_lever_arms(int32_t n_mounts, double* boresight, double* lever, const uint8_t* fixed, const int32_t* cam_mount);
     int shared_info(int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block) const;
+    // UV <-> UV factors (sba_solver_pairs.inc)
+    int add_uv_pairs(int32_t n, const int32_t* cam1, const int32_t* cam2, const double* uv1, const double* uv2, const double* info1, const double* info2);
+    int set_pair_loss(int32_t kind, double a);
+    int evaluate_pairs(double* res4, double* jac48);
     int set_poses(double* raxis, double* t, int32_t n, const int32_t* model, const uint8_t* fixed, const uint8_t* kind);
     int set_points(double* xyz, int32_t n, const uint8_t* fixed);
     int add_observations(int32_t n, const int32_t* cam, const int32_t* pt, const double* uv, const double* info);
@@ -134,6 +138,10 @@ private:
     double* h_mount_b = nullptr; double* h_mount_l = nullptr; int32_t Nmt = 0;
     std::vector<uint8_t> mount_fixed; std::vector<int32_t> cam_mount;
     int32_t Nce = 0;
+    std::vector<int32_t> pair_c; std::vector<double> pair_px, pair_w; bool pair_has_info = false;
+    int32_t pair_loss_kind = 0; double pair_loss_scale = 1.0;
+    std::vector<int32_t> pblk_i_h, pblk_j_h;          // distinct camera pairs of the factors
+    int upload_pair_tables();
     std::vector<int32_t> model_block, mount_block;     // first pseudo-camera of a free model / mounting, -1: constant
     int plan_shared_blocks();                          // groups + pseudo-cameras (before the allocations of finalize)
     int upload_shared_tables();                        // device side of the shared blocks (after the allocations)

@@ -150,6 +150,26 @@ class SBASolver:
         self._keep.update(mount_b=boresight, mount_l=lever, cam_mount=cm, mount_fixed=fx)
         self._check(self._lib.sba_set_lever_arms(self._h, n, _ptr(boresight), _ptr(lever), _ptr(fx), _ptr(cm)))
 
+    def add_uv_pairs(self, cam1, cam2, uv1, uv2, info1=None, info2=None):
+        """UV <-> UV cross-projection factors (addCrossProjectionCostFunction): uv1, uv2 (n, 2), info (n, 2, 2) or None."""
+        cam1 = np.ascontiguousarray(cam1, dtype=np.int32); cam2 = np.ascontiguousarray(cam2, dtype=np.int32)
+        uv1 = _f64(uv1); uv2 = _f64(uv2)
+        i1 = None if info1 is None else _f64(info1); i2 = None if info2 is None else _f64(info2)
+        if cam2.size != cam1.size or uv1.size != 2 * cam1.size or uv2.size != 2 * cam1.size:
+            raise ValueError("uv pairs: sizes disagree")
+        self._n_pairs = getattr(self, "_n_pairs", 0) + cam1.size
+        self._check(self._lib.sba_add_uv_pairs(self._h, cam1.size, _ptr(cam1), _ptr(cam2), _ptr(uv1), _ptr(uv2), _ptr(i1), _ptr(i2)))
+
+    def set_pair_loss(self, kind, a=1.0):
+        kinds = {None: 0, "none": 0, "huber": 1, "cauchy": 2, "arctan": 3}
+        self._check(self._lib.sba_set_pair_loss(self._h, kinds.get(kind, kind), float(a)))
+
+    def evaluate_pairs(self):
+        n = getattr(self, "_n_pairs", 0)
+        r = np.empty((n, 4)); j = np.empty((n, 4, 12))
+        self._check(self._lib.sba_evaluate_pairs(self._h, _ptr(r), _ptr(j)))
+        return r, j
+
     def shared_info(self):
         """Layout of the reduced camera system: extended cameras, groups, first pseudo-camera of every model / mounting (-1: constant)."""
         n_ext, n_g = C.c_int32(), C.c_int32()

@@ -229,6 +229,12 @@ def load_into(solver, scene, copy=True):
         solver.set_lever_arms(solver.mount_b, solver.mount_l, scene["cam_mount"], scene.get("mount_fixed"))
     solver.set_points(pts, scene["pt_fixed"])
     solver.add_observations(scene["obs_cam"], scene["obs_pt"], scene["obs_uv"], scene["obs_info"])
+    if scene.get("pair_cam") is not None and len(scene["pair_cam"]):
+        pc = np.asarray(scene["pair_cam"], dtype=np.int32).reshape(-1, 2); puv = np.asarray(scene["pair_uv"], dtype=np.float64).reshape(-1, 4)
+        pinfo = None if scene.get("pair_info") is None else np.asarray(scene["pair_info"], dtype=np.float64).reshape(-1, 8)
+        solver.add_uv_pairs(pc[:, 0], pc[:, 1], puv[:, :2], puv[:, 2:], None if pinfo is None else pinfo[:, :4], None if pinfo is None else pinfo[:, 4:])
+        if scene.get("loss"):
+            solver.set_pair_loss(scene["loss"], scene.get("loss_a", 1.0))
     if scene["prior_kind"].size:
         solver.add_priors(scene["prior_kind"], scene["prior_index"], scene["prior_A"], scene["prior_b"])
     return raxis, t, pts

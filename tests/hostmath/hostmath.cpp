@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include "../../steviapp_b200/csrc/sba_math.cuh"
+#include "../../steviapp_b200/csrc/sba_jet.cuh"
 
 extern "C" {
 
@@ -85,5 +86,36 @@ int hm_eval_leverarm(int32_t n, const double* r, const double* t, const double* 
 int hm_inv6(const double* A, double* Ai) { return sba::inv6_spd(A, Ai) ? 0 : 1; }
 int hm_inv3(const double* H6, double* Hi6) { return sba::inv3_sym(H6, Hi6) ? 0 : 1; }
 void hm_pose_cache(const double* r, const double* t, double* out24) { sba::pose_cache(r, t, out24); }
+
+
+// UV <-> UV factor (sba_jet.cuh: the functor the pair kernels run): raw residuals (4) and the Jacobian 4 x 28 with respect to
+// pose1 (6), pose2 (6) and the 8 intrinsic columns of camera 1's and camera 2's model (chain rule through the view rays)
+void hm_uv2uv(int32_t n, const double* r1, const double* t1, const double* r2, const double* t2, const double* intr1, const double* intr2,
+              const double* uv, const double* info, double* res, double* jac) {
+    typedef sba::DJet<18> J;
+    for (int32_t k = 0; k < n; k++) {
+        double d1[3], d2[3], dd1[24], dd2[24];
+        sba::dir_from_uv_jac(uv[4 * k], uv[4 * k + 1], intr1, d1, dd1);
+        sba::dir_from_uv_jac(uv[4 * k + 2], uv[4 * k + 3], intr2, d2, dd2);
+        J a[3], b[3], c[3], d[3], e[3], f[3], out[4];
+        for (int i = 0; i < 3; i++) {
+            a[i] = J(r1[3 * k + i], i); b[i] = J(t1[3 * k + i], 3 + i); c[i] = J(r2[3 * k + i], 6 + i); d[i] = J(t2[3 * k + i], 9 + i);
+            e[i] = J(d1[i], 12 + i); f[i] = J(d2[i], 15 + i);
+        }
+        sba::uv2uv_residual<J>(a, b, c, d, e, f, info ? info + 8 * k : nullptr, info ? info + 8 * k + 4 : nullptr, out);
+        for (int i = 0; i < 4; i++) {
+            res[4 * k + i] = out[i].a;
+            for (int j = 0; j < 12; j++) jac[(4 * k + i) * 28 + j] = out[i].v[j];
+            for (int j = 0; j < 8; j++) {
+                jac[(4 * k + i) * 28 + 12 + j] = out[i].v[12] * dd1[j] + out[i].v[13] * dd1[8 + j] + out[i].v[14] * dd1[16 + j];
+                jac[(4 * k + i) * 28 + 20 + j] = out[i].v[15] * dd2[j] + out[i].v[16] * dd2[8 + j] + out[i].v[17] * dd2[16 + j];
+            }
+        }
+    }
+}
+void hm_loss(int kind, double a, double s, double* rho3, double* corr3) {
+    sba::loss_rho(kind, a, s, rho3);
+    sba::loss_corrector(s, rho3, corr3, corr3 + 1, corr3 + 2);
+}
 
 }
