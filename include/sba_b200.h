@@ -85,6 +85,12 @@ typedef struct sba_options {
                                          (rebuilds A, C from Pbar: 60 B/obs), else as 1;
                                      3 = explicit S forced (error if it cannot be built) */
     int32_t verbose;
+    int32_t linear_solver;        /* reduced solve: 0 = SCHUR_JACOBI-preconditioned CG (ceres::ITERATIVE_SCHUR), 1 = Cholesky of the explicit
+                                     reduced camera system on the device -- the reference's default solver type, ceres::SPARSE_SCHUR
+                                     (modularsbasolver.h:672, modularsbasolver.cpp:898), is a factorisation of the same S; needs
+                                     operator_mode 0 / 3, one GPU */
+    double pcg_eta;               /* 0: CG to pcg_rel_tol.  > 0: inexact Newton as Ceres runs ITERATIVE_SCHUR (eta = 0.1 by default there): CG stops at
+                                     sqrt(r.z / r0.z0) <= max(pcg_eta, pcg_rel_tol) -- a throughput setting, not a parity one */
 } sba_options;
 
 #define SBA_MAX_HISTORY 512
@@ -177,6 +183,13 @@ int sba_set_pair_loss(sba_solver* s, int32_t kind, double a);
 /* raw residuals (4 per factor) and raw pose Jacobians (4 x 12 row-major: d/d rAxis1, t1, rAxis2, t2) before the loss;
  * ceres::Problem::Evaluate on those residual blocks.  Parity hook. */
 int sba_evaluate_pairs(sba_solver* s, double* res4, double* jac48);
+
+/* ModularSBASolver::std_step (modularsbasolver.cpp:952-1004): marginal covariance of the point blocks at the current
+ * parameters -- ceres::Covariance over the (pos, pos) pairs LandmarksSBAModule::requestUncertainty asks for
+ * (sbamodules/landmarkssbamodule.cpp:264-297).  cov9 = n_pts x 3 x 3 row-major (zeros for constant points).  From the
+ * undamped normal equations by a dense Cholesky + selected inverse of the reduced camera system on the device; returns
+ * SBA_ERR_NUMERIC ("Failed to compute covariance matrix", the reference's message) when the system is rank deficient. */
+int sba_point_covariances(sba_solver* s, double* cov9);
 
 /* Pose blocks: getNodeForFrame + initManagedParameters
  * (modularsbasolver.cpp:233-306,804-870).  raxis/t are 3*n AoS, caller-owned,

@@ -28,7 +28,7 @@ EXPORTS = [
     "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
     "sba_pushbroom_equivalent_uv",
     "sba_set_intrinsics_blocks", "sba_add_intrinsics_priors", "sba_set_sensor_offsets", "sba_set_lever_arms", "sba_shared_info",
-    "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
+    "sba_point_covariances", "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
 ]
 
 
@@ -40,6 +40,7 @@ class SbaOptions(C.Structure):
         ("min_lm_diagonal", C.c_double), ("max_lm_diagonal", C.c_double), ("min_relative_decrease", C.c_double),
         ("jacobi_scaling", C.c_int32), ("pcg_rel_tol", C.c_double), ("pcg_max_iters", C.c_int32),
         ("pcg_check_every", C.c_int32), ("operator_mode", C.c_int32), ("verbose", C.c_int32),
+        ("linear_solver", C.c_int32), ("pcg_eta", C.c_double),
     ]
 
 
@@ -123,6 +124,7 @@ def load():
     lib.sba_add_uv_pairs.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp]
     lib.sba_set_pair_loss.argtypes = [vp, i32, dbl]
     lib.sba_evaluate_pairs.argtypes = [vp, vp, vp]
+    lib.sba_point_covariances.argtypes = [vp, vp]
     lib.sba_bal_open.argtypes = [C.c_char_p, C.POINTER(vp)]
     lib.sba_bal_close.argtypes = [vp]
     lib.sba_bal_close.restype = None

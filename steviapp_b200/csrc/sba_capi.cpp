@@ -38,6 +38,8 @@ void sba_default_options(sba_options* o) {
     o->pcg_check_every = 1;
     o->operator_mode = 0;
     o->verbose = 0;
+    o->linear_solver = 0;
+    o->pcg_eta = 0.0;
 }
 
 int sba_create(const sba_options* o, sba_solver** out) {
@@ -70,6 +72,7 @@ int sba_add_uv_pairs(sba_solver* s, int32_t n, const int32_t* cam1, const int32_
                      const double* info1, const double* info2) { GUARD(s); return s->impl.add_uv_pairs(n, cam1, cam2, uv1, uv2, info1, info2); }
 int sba_set_pair_loss(sba_solver* s, int32_t kind, double a) { GUARD(s); return s->impl.set_pair_loss(kind, a); }
 int sba_evaluate_pairs(sba_solver* s, double* res4, double* jac48) { GUARD(s); return s->impl.evaluate_pairs(res4, jac48); }
+int sba_point_covariances(sba_solver* s, double* cov9) { GUARD(s); return s->impl.point_covariances(cov9); }
 int sba_shared_info(const sba_solver* s, int32_t* n_ext, int32_t* n_groups, int32_t* model_block, int32_t* mount_block) {
     GUARD(s); return s->impl.shared_info(n_ext, n_groups, model_block, mount_block);
 }

@@ -321,6 +321,12 @@ void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t s
 void launch_explicit_gather(const DevProblem& P, double* y, cudaStream_t st);         // y = sum of the partials (test hook; PCG folds them in k_pcg_A)
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st);
+// dense Cholesky of the explicit reduced system: direct solve and point covariances (sba_kernels_dense.cu)
+void launch_dense_from_tiles(const DevProblem& P, double* D, int n, cudaStream_t st);   // P with Nc = extended cameras; n = padded side (multiple of 384)
+int dense_cholesky(double* D, int n, double* Linv_all, double* work, int* flag, cudaStream_t st);   // in place, lower factor; returns launches
+int dense_solve(const double* L, int n, const double* Linv_all, double* x, cudaStream_t st);
+int dense_inverse(const double* L, int n, const double* Linv_all, double* Z, double* Sinv, double* work, cudaStream_t st);
+void launch_point_covariance(const DevProblem& P, const double* Sinv, int n, double* cov9, cudaStream_t st);
 // UV <-> UV factors (sba_kernels_pairs.cu)
 void launch_pair_eval(const DevProblem& P, int store, cudaStream_t st);          // residuals / corrected Jacobians (store) and the cost, added to SC_COST_PRIOR_CAM
 void launch_pair_camera_blocks(const DevProblem& P, cudaStream_t st);           // Hcc, gc (+ sh_H, sh_g, pair_border with free intrinsics)

@@ -1,0 +1,270 @@
+// sba_kernels_dense.cu -- dense FP64 Cholesky of the explicit reduced camera system on the device: the DIRECT reduced solve
+// (the reference's default solver type is ceres::SPARSE_SCHUR, i.e. a Cholesky factorisation of S, not CG:
+// modularsbasolver.h:672, modularsbasolver.cpp:898) and the selected inverse behind the point covariances of
+// ModularSBASolver::std_step (modularsbasolver.cpp:952-1004; pairs requested by landmarkssbamodule.cpp:264-297).
+//
+// S (6 Nce scalars per side, 10 752 for the Venice shape) is already explicit in HBM as 384x384 tiles; it is copied into a
+// dense row-major matrix and factorised S = L L^T by a right-looking blocked algorithm with 64x64 blocks:
+//   per block column:  one CTA factorises the diagonal block in shared memory and inverts the triangular factor;
+//                      panel  L21 = A21 inv(L11)^T  and trailing update  A22 -= L21 L21^T  are tile GEMMs.
+// The same tile GEMM (64x64 tile per CTA, 4x4 micro-tile per thread, K staged through shared memory in steps of 16) carries the
+// triangular inverse Z = L^-1 and S^-1 = Z^T Z.  This is the one place on the path with a real contraction (n^3 / 3 flops);
+// FP64 on the CUDA cores.  No atomics: deterministic.
+#include <algorithm>
+
+#include "sba_kernel_util.cuh"
+
+namespace sba {
+
+constexpr int DB = 64;        // block size
+
+// tiles (upper block triangle, diagonal tiles carry S_ii / 2 on their block diagonal and zeros below) -> dense symmetric
+// row-major n x n; rows / columns whose diagonal is zero (constant cameras without damping) get a unit diagonal
+__global__ void __launch_bounds__(256) k_dense_from_tiles(DevProblem P, double* __restrict__ D, int n) {
+    const int t = blockIdx.x;
+    const int I = P.ex_tile_I[t], J = P.ex_tile_J[t];
+    const double* T = P.ex_Sown + (size_t)t * EX_TD * EX_TD;
+    for (int e = threadIdx.x; e < EX_TD * EX_TD; e += blockDim.x) {
+        const int r = e / EX_TD, c = e - r * EX_TD;
+        const double v = T[e];
+        const size_t gr = (size_t)EX_TD * I + r, gc = (size_t)EX_TD * J + c;
+        if (I != J) { D[gr * n + gc] = v; D[gc * n + gr] = v; }
+        else {
+            // upper part of the diagonal tile holds S, its 6x6 diagonal blocks hold S_ii / 2 in full (both triangles)
+            const bool same_block = r / 6 == c / 6;
+            if (same_block) D[gr * n + gc] = 2.0 * v;
+            else if (c > r) { D[gr * n + gc] = v; D[gc * n + gr] = v; }
+        }
+    }
+}
+__global__ void k_dense_fix_diag(double* D, int n, int n_live) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i >= n_live || D[(size_t)i * n + i] == 0.0) D[(size_t)i * n + i] = 1.0;   // padding rows / constant blocks: decoupled unit rows
+}
+
+// C (M x N, ldc) = beta C + alpha op(A) op(B); 64x64 tile per CTA.  K range per tile by kmode:
+//  0 full; 1 k >= max(bi, bj) blocks (Z^T Z with lower-triangular Z); 2 lower tiles only (bj <= bi), full K; 3 k >= bj blocks
+template <bool AT, bool BT>
+__global__ void __launch_bounds__(256) k_dgemm(const double* __restrict__ A, int lda, const double* __restrict__ B, int ldb,
+                                               double* __restrict__ C, int ldc, int K, double alpha, double beta, int kmode) {
+    __shared__ double As[16][DB + 4], Bs[16][DB + 4];
+    const int bi = blockIdx.y, bj = blockIdx.x;
+    if (kmode == 2 && bj > bi) return;
+    int k0 = 0;
+    if (kmode == 1) k0 = DB * max(bi, bj);
+    if (kmode == 3) k0 = DB * bj;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+    const int m0 = DB * bi, n0 = DB * bj;
+    for (int k = k0; k < K; k += 16) {
+        // stage A (64 x 16) and B (16 x 64): 1024 elements each, 4 per thread
+#pragma unroll
+        for (int e = threadIdx.x; e < 1024; e += 256) {
+            if (AT) { const int kk = e >> 6, m = e & 63; As[kk][m] = A[(size_t)(k + kk) * lda + m0 + m]; }
+            else { const int m = e >> 4, kk = e & 15; As[kk][m] = A[(size_t)(m0 + m) * lda + k + kk]; }
+            if (BT) { const int nn = e >> 4, kk = e & 15; Bs[kk][nn] = B[(size_t)(n0 + nn) * ldb + k + kk]; }
+            else { const int kk = e >> 6, nn = e & 63; Bs[kk][nn] = B[(size_t)(k + kk) * ldb + n0 + nn]; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; kk++) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) { a[i] = As[kk][ty + 16 * i]; b[i] = Bs[kk][tx + 16 * i]; }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) acc[i][j] += a[i] * b[j];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            double* c = C + (size_t)(m0 + ty + 16 * i) * ldc + n0 + tx + 16 * j;
+            *c = (beta == 0.0 ? 0.0 : beta * *c) + alpha * acc[i][j];
+        }
+}
+
+// one CTA: Cholesky of the 64x64 diagonal block at D[k0, k0] in shared memory (lower factor written back, upper part zeroed)
+// and the inverse of the factor into Linv (64x64 row-major, lower triangular).  flag set when a pivot is not positive.
+__global__ void __launch_bounds__(DB) k_potrf_block(double* __restrict__ D, int n, int k0, double* __restrict__ Linv, int* flag) {
+    __shared__ double L[DB][DB + 1];
+    __shared__ int bad;
+    const int t = threadIdx.x;
+    if (t == 0) bad = 0;
+    for (int r = 0; r < DB; r++) L[r][t] = D[(size_t)(k0 + r) * n + k0 + t];
+    __syncthreads();
+    for (int j = 0; j < DB; j++) {
+        if (t == 0) {
+            const double d = L[j][j];
+            if (!(d > 0.0)) { bad = 1; L[j][j] = 1.0; } else L[j][j] = sqrt(d);
+        }
+        __syncthreads();
+        if (t > j) L[t][j] /= L[j][j];
+        __syncthreads();
+        if (t > j) for (int c = j + 1; c <= t; c++) L[t][c] -= L[t][j] * L[c][j];   // row t of the trailing lower triangle
+        __syncthreads();
+    }
+    for (int r = 0; r < DB; r++) D[(size_t)(k0 + r) * n + k0 + t] = t <= r ? L[r][t] : 0.0;
+    // inverse: thread t solves L x = e_t (column t of L^-1)
+    double x[DB];
+    for (int i = 0; i < DB; i++) {
+        double s = i == t ? 1.0 : 0.0;
+        for (int k = t; k < i; k++) s -= L[i][k] * x[k];
+        x[i] = i < t ? 0.0 : s / L[i][i];
+    }
+    for (int i = 0; i < DB; i++) Linv[(size_t)i * DB + t] = x[i];
+    if (t == 0 && bad) *flag = 1;
+}
+
+// in-place dense Cholesky, lower factor; Linv_all: (n / 64) inverse diagonal blocks; work: n x 64 panel scratch.  Returns launches.
+int dense_cholesky(double* D, int n, double* Linv_all, double* work, int* flag, cudaStream_t st) {
+    const int NB = n / DB;
+    int launches = 0;
+    for (int kb = 0; kb < NB; kb++) {
+        const int k0 = DB * kb, rem = NB - kb - 1;
+        double* Li = Linv_all + (size_t)kb * DB * DB;
+        k_potrf_block<<<1, DB, 0, st>>>(D, n, k0, Li, flag);
+        launches++;
+        if (!rem) break;
+        double* A21 = D + (size_t)(k0 + DB) * n + k0;
+        // panel: L21 = A21 Linv^T (through the scratch panel: the GEMM is not in place)
+        k_dgemm<false, true><<<dim3(1, rem), 256, 0, st>>>(A21, n, Li, DB, work, DB, DB, 1.0, 0.0, 0);
+        cudaMemcpy2DAsync(A21, (size_t)n * sizeof(double), work, DB * sizeof(double), DB * sizeof(double), (size_t)rem * DB, cudaMemcpyDeviceToDevice, st);
+        // trailing update, lower tiles: A22 -= L21 L21^T
+        k_dgemm<false, true><<<dim3(rem, rem), 256, 0, st>>>(A21, n, A21, n, D + (size_t)(k0 + DB) * n + k0 + DB, n, DB, -1.0, 1.0, 2);
+        launches += 3;
+    }
+    return launches;
+}
+
+// x = S^-1 b with the factor: forward and backward substitution by blocks (one small CTA per block step)
+__global__ void __launch_bounds__(4 * DB) k_trsv_block(const double* __restrict__ L, int n, const double* __restrict__ Linv_all, double* x, int kb, int backward) {
+    __shared__ double s[DB], part[4][DB];
+    const int t = threadIdx.x & (DB - 1), h = threadIdx.x / DB, k0 = DB * kb;   // four threads per row split the sum, folded in fixed order
+    double acc = 0.0;
+    if (!backward) { for (int j = h; j < k0; j += 4) acc += L[(size_t)(k0 + t) * n + j] * x[j]; }
+    else { for (int j = k0 + DB + h; j < n; j += 4) acc += L[(size_t)j * n + k0 + t] * x[j]; }
+    part[h][t] = acc;
+    __syncthreads();
+    if (h == 0) s[t] = x[k0 + t] - ((part[0][t] + part[1][t]) + (part[2][t] + part[3][t]));
+    __syncthreads();
+    if (h != 0) return;
+    const double* Li = Linv_all + (size_t)kb * DB * DB;
+    double v = 0.0;
+    if (!backward) { for (int j = 0; j <= t; j++) v += Li[(size_t)t * DB + j] * s[j]; }
+    else { for (int j = t; j < DB; j++) v += Li[(size_t)j * DB + t] * s[j]; }
+    x[k0 + t] = v;
+}
+int dense_solve(const double* L, int n, const double* Linv_all, double* x, cudaStream_t st) {
+    const int NB = n / DB;
+    for (int kb = 0; kb < NB; kb++) k_trsv_block<<<1, 4 * DB, 0, st>>>(L, n, Linv_all, x, kb, 0);
+    for (int kb = NB - 1; kb >= 0; kb--) k_trsv_block<<<1, 4 * DB, 0, st>>>(L, n, Linv_all, x, kb, 1);
+    return 2 * NB;
+}
+
+// Z = L^-1 (lower triangular, n x n, zero above the diagonal blocks) and Sinv = Z^T Z.  Z and Sinv are caller buffers; work: 64 x n.
+__global__ void k_copy_block(const double* __restrict__ src, int lds, double* __restrict__ dst, int ldd) {
+    for (int e = threadIdx.x; e < DB * DB; e += blockDim.x) { const int r = e / DB, c = e - r * DB; dst[(size_t)r * ldd + c] = src[(size_t)r * lds + c]; }
+}
+int dense_inverse(const double* L, int n, const double* Linv_all, double* Z, double* Sinv, double* work, cudaStream_t st) {
+    const int NB = n / DB;
+    int launches = 0;
+    cudaMemsetAsync(Z, 0, (size_t)n * n * sizeof(double), st);
+    for (int ib = 0; ib < NB; ib++) {
+        const double* Li = Linv_all + (size_t)ib * DB * DB;
+        k_copy_block<<<1, 256, 0, st>>>(Li, DB, Z + (size_t)(DB * ib) * n + DB * ib, n);   // Z_ii = inv(L_ii)
+        launches++;
+        if (!ib) continue;
+        // T = L_{i, 0:i} Z_{0:i, 0:i} (64 x 64 i), K range of column block j starts at j (Z lower triangular); Z_{i, 0:i} = -inv(L_ii) T
+        k_dgemm<false, false><<<dim3(ib, 1), 256, 0, st>>>(L + (size_t)(DB * ib) * n, n, Z, n, work, n, DB * ib, 1.0, 0.0, 3);
+        k_dgemm<false, false><<<dim3(ib, 1), 256, 0, st>>>(Li, DB, work, n, Z + (size_t)(DB * ib) * n, n, DB, -1.0, 0.0, 0);
+        launches += 2;
+    }
+    k_dgemm<true, false><<<dim3(NB, NB), 256, 0, st>>>(Z, n, Z, n, Sinv, n, n, 1.0, 0.0, 1);   // Sinv = Z^T Z
+    return launches + 1;
+}
+
+// ---------------------------------------------------------------------------
+// point covariances: Cov_p = Hinv + sum_{e, f} (W_e Hinv)^T Sinv[e, f] (W_f Hinv) over the reduced-side blocks e, f the point
+// touches -- its observations' cameras (W = Jc^T A, 6 x 3) and the shared groups (W_g^T, 8 x 3).  One WARP per point: the
+// lanes split the (e, f) pairs, a fixed shuffle tree sums the nine entries.  Undamped blocks (the caller linearised with
+// zero damping): (J^T J)^-1 restricted to the point, what ceres::Covariance returns for the pair (block, block).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void cov_entry(const DevProblem& P, int p, int q0, int k, int e, const double* Hi, int* ext, double* M /*up to 8 x 3*/, int* rows) {
+    if (e < k) {   // observation e of the point: M = Jc^T (A Hinv), Jc = [C | -A], C = A [X - t]x Q^T
+        const int q = q0 + e;
+        const int cam = P.q_cam[q];
+        const size_t Nq = (size_t)P.Nq;
+        double A[6];
+        for (int i = 0; i < 6; i++) A[i] = P.qA[(size_t)i * Nq + q];
+        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+        const double* Q = P.cam_Q + 12 * (size_t)cam;
+        const double* X = P.pts + 4 * (size_t)p;
+        const double d[3] = {X[0] - (cc[9] - Q[9]), X[1] - (cc[10] - Q[10]), X[2] - (cc[11] - Q[11])};   // X - t (body)
+        double Jc[12];
+        for (int r = 0; r < 2; r++) {
+            const double a0 = A[3 * r], a1 = A[3 * r + 1], a2 = A[3 * r + 2];
+            const double w0 = a1 * d[2] - a2 * d[1], w1 = a2 * d[0] - a0 * d[2], w2 = a0 * d[1] - a1 * d[0];
+            for (int c = 0; c < 3; c++) { Jc[6 * r + c] = w0 * Q[3 * c] + w1 * Q[3 * c + 1] + w2 * Q[3 * c + 2]; Jc[6 * r + 3 + c] = -A[3 * r + c]; }
+        }
+        double AH[6];   // A Hinv (2 x 3)
+        for (int r = 0; r < 2; r++)
+            for (int c = 0; c < 3; c++) AH[3 * r + c] = A[3 * r] * Hi[c] + A[3 * r + 1] * Hi[3 + c] + A[3 * r + 2] * Hi[6 + c];
+        const bool fixed = P.cam_fixed[cam];
+        for (int a = 0; a < 6; a++)
+            for (int c = 0; c < 3; c++) M[3 * a + c] = fixed ? 0.0 : Jc[a] * AH[c] + Jc[6 + a] * AH[3 + c];
+        *ext = 6 * cam; *rows = 6;
+    } else {       // shared group: M = W_g^T Hinv, rows = its 8 columns (contiguous in the extended layout)
+        const int g = e - k;
+        const double* W = P.sh_W + ((size_t)g * P.Np + p) * 24;
+        for (int c8 = 0; c8 < 8; c8++)
+            for (int c = 0; c < 3; c++) M[3 * c8 + c] = P.grp_live[8 * g + c8] ? W[c8] * Hi[c] + W[8 + c8] * Hi[3 + c] + W[16 + c8] * Hi[6 + c] : 0.0;
+        *ext = 6 * P.grp_blk[g]; *rows = 8;
+    }
+}
+__global__ void __launch_bounds__(256) k_point_covariance(DevProblem P, const double* __restrict__ Sinv, int n, double* __restrict__ cov9) {
+    const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (p >= P.Np) return;
+    const double* Hp = P.Hinv + 8 * (size_t)p;
+    const double Hi[9] = {Hp[0], Hp[1], Hp[2], Hp[1], Hp[3], Hp[4], Hp[2], Hp[4], Hp[5]};
+    const int k = P.pt_off[p + 1] - P.pt_off[p], q0 = P.pt_q0[p];
+    const int ne = k + P.Ng;
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (!P.pt_fixed[p])
+        for (long long pr = lane; pr < (long long)ne * ne; pr += 32) {
+            const int e = (int)(pr / ne), f = (int)(pr - (long long)e * ne);
+            double Me[24], Mf[24];
+            int xe, xf, re, rf;
+            cov_entry(P, p, q0, k, e, Hi, &xe, Me, &re);
+            cov_entry(P, p, q0, k, f, Hi, &xf, Mf, &rf);
+            for (int a = 0; a < re; a++) {
+                double t[3] = {0, 0, 0};   // row a of Sinv[e, f] times Mf
+                for (int b = 0; b < rf; b++) {
+                    const double s = Sinv[(size_t)(xe + a) * n + xf + b];
+                    t[0] += s * Mf[3 * b]; t[1] += s * Mf[3 * b + 1]; t[2] += s * Mf[3 * b + 2];
+                }
+                for (int c = 0; c < 3; c++) { acc[3 * c] += Me[3 * a + c] * t[0]; acc[3 * c + 1] += Me[3 * a + c] * t[1]; acc[3 * c + 2] += Me[3 * a + c] * t[2]; }
+            }
+        }
+    for (int i = 0; i < 9; i++) acc[i] = warp_sum(acc[i]);
+    if (lane == 0) for (int i = 0; i < 9; i++) cov9[9 * (size_t)p + i] = (P.pt_fixed[p] ? 0.0 : Hi[i]) + acc[i];
+}
+
+void launch_dense_from_tiles(const DevProblem& P, double* D, int n, cudaStream_t st) {
+    cudaMemsetAsync(D, 0, (size_t)n * n * sizeof(double), st);
+    if (P.ex_nown) k_dense_from_tiles<<<P.ex_nown, 256, 0, st>>>(P, D, n);
+    k_dense_fix_diag<<<cdiv(n, 256), 256, 0, st>>>(D, n, 6 * P.Nc);
+}
+void launch_point_covariance(const DevProblem& P, const double* Sinv, int n, double* cov9, cudaStream_t st) {
+    if (P.Np) k_point_covariance<<<cdiv(P.Np * 32, 256), 256, 0, st>>>(P, Sinv, n, cov9);
+}
+
+}  // namespace sba

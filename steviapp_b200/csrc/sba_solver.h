@@ -81,6 +81,8 @@ public:
     int add_uv_pairs(int32_t n, const int32_t* cam1, const int32_t* cam2, const double* uv1, const double* uv2, const double* info1, const double* info2);
     int set_pair_loss(int32_t kind, double a);
     int evaluate_pairs(double* res4, double* jac48);
+    int point_covariances(double* cov9);        // ModularSBASolver::std_step (sba_solver_pairs.inc)
+    int direct_solve();                         // Cholesky of the explicit S -> pcg_x (opt.linear_solver == 1)
     int set_poses(double* raxis, double* t, int32_t n, const int32_t* model, const uint8_t* fixed, const uint8_t* kind);
     int set_points(double* xyz, int32_t n, const uint8_t* fixed);
     int add_observations(int32_t n, const int32_t* cam, const int32_t* pt, const double* uv, const double* info);
@@ -138,6 +140,8 @@ private:
     double* h_mount_b = nullptr; double* h_mount_l = nullptr; int32_t Nmt = 0;
     std::vector<uint8_t> mount_fixed; std::vector<int32_t> cam_mount;
     int32_t Nce = 0;
+    double* dn_D = nullptr; double* dn_Linv = nullptr; double* dn_work = nullptr; double* dn_x = nullptr; int dn_n = 0;   // dense factor of S (lazy)
+    int dense_alloc();
     std::vector<int32_t> pair_c; std::vector<double> pair_px, pair_w; bool pair_has_info = false;
     int32_t pair_loss_kind = 0; double pair_loss_scale = 1.0;
     std::vector<int32_t> pblk_i_h, pblk_j_h;          // distinct camera pairs of the factors

@@ -170,6 +170,13 @@ class SBASolver:
         self._check(self._lib.sba_evaluate_pairs(self._h, _ptr(r), _ptr(j)))
         return r, j
 
+    def point_covariances(self):
+        """std_step: (n_pts, 3, 3) marginal covariances of the point blocks at the current (device-resident) parameters."""
+        self.finalize()
+        cov = np.empty((self.sizes()["n_pts"], 3, 3))
+        self._check(self._lib.sba_point_covariances(self._h, _ptr(cov)))
+        return cov
+
     def shared_info(self):
         """Layout of the reduced camera system: extended cameras, groups, first pseudo-camera of every model / mounting (-1: constant)."""
         n_ext, n_g = C.c_int32(), C.c_int32()
