@@ -15,7 +15,8 @@ from steviapp_b200 import SBASolver, synthetic, comm_unique_id
 
 shape = sys.argv[1] if len(sys.argv) > 1 else "ladybug"
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 4
-only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
+only = sys.argv[3].split(",") if len(sys.argv) > 3 and sys.argv[3] != "all" else None
+ext = len(sys.argv) > 4 and sys.argv[4] == "ext"   # free intrinsics + offsets + free lever arms + UV <-> UV factors (explicit system only)
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -25,6 +26,17 @@ if shape.startswith("cams"):   # e.g. cams300: several tiles, band structure
     sc = synthetic.make_scene(None, n_cams=n, n_pts=100 * n, n_obs=500 * n, seed=7)
 else:
     sc = synthetic.make_scene(shape)
+if ext:
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+    import test_gpu_shared as tgs
+    import test_pairs_host as tph
+    rng = np.random.default_rng(11)
+    pairs = tph.pair_scene(shape if not shape.startswith("cams") else "ladybug", n_pairs=400, outliers=0.05)
+    sc = tgs.with_pose_priors(tgs.add_rig(sc, rng, offsets=True, n_mounts=2))
+    sc["intrinsics"] = tgs.perturbed_intrinsics(sc, rng); sc["intr_fixed_mask"] = np.array([0x10], np.uint8)
+    if not shape.startswith("cams"):
+        sc["pair_cam"], sc["pair_uv"], sc["loss"] = pairs["pair_cam"], pairs["pair_uv"], "huber"
+    only = [m for m in (only or ["explicit+peer", "explicit+nccl"]) if m.startswith("explicit")]
 sh = synthetic.shard_scene(sc, rank, world)
 
 r1 = None

@@ -406,6 +406,23 @@ def test_two_gpu_block_sparse_panels():
     assert res["ok"] and all(i["sparse"] == 1 and i["persistent_pcg"] == 1 for i in res["modes"][0]["info"])
 
 
+def test_two_gpu_shared_blocks_and_pair_factors():
+    """2 GPUs with free intrinsics, sensor offsets, free lever arms and UV <-> UV factors: the border / Schur terms of the shared
+    blocks are partial sums over a rank's points (one all-reduce), the factor terms are replicated and added once."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29535", os.path.join(root, "scripts", "multigpu_check.py"), "ladybug", "4", "all", "ext"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=280)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    res = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
+    assert res["ok"] and {m["mode"] for m in res["modes"]} == {"explicit+peer", "explicit+nccl"}
+
+
 def test_venice_scale_explicit_tiles_against_implicit_operator(monkeypatch):
     """Full BASELINE size: the explicit reduced camera system (406 dense tiles built from 11.6 M point-pair contributions) and
     the implicit operator (two passes over the 5 M observations) are independent code paths for the same S; they must agree
