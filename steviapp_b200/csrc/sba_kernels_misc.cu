@@ -205,51 +205,46 @@ void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* l
 }
 
 // ---------------------------------------------------------------------------
-// K5 batched multi-view DLT: EIGHT lanes per point (a point has ~5 views: one view per lane, strided for longer tracks), so
-// the dependent chain index -> camera record -> normal equations of the views of a point runs in parallel instead of
-// serially in one thread (the kernel is bound by that latency, not by bytes: 20 B per view stream from HBM, the 96-byte
-// camera records come from L1 / L2).  The nine sums (packed 3x3 + rhs) are folded by a fixed xor-shuffle tree over the 8
-// lanes -- deterministic -- and lane 0 of the group solves the 3x3 system in closed form.
-// SURVEY 8(d) bytes: 72 B per view (pose + ray) + 24 B per point.
+// K5 batched multi-view DLT: thread per point, inhomogeneous normal equations accumulated over its views in registers,
+// closed-form symmetric 3x3 solve.  Per view: 16 B pixel + 4 B camera index streamed, the camera record (Rt, t: 96 B = three
+// 256-bit loads) gathered from L1 / L2; the intrinsics record is re-read only when the camera MODEL changes between two views
+// of the point (one model per Camera datablock in the reference: almost never) -- the kernel is bound by load instructions /
+// L1 wavefronts, not by bytes.  24 B + 1 B out per point.  SURVEY 8(d) bytes: 72 B per view (pose + ray) + 24 B per point.
+// (Eight lanes per point with a shuffle tree was measured 2x slower: 3.6 ms vs 1.8 ms for 10.9 M points.)
 // ---------------------------------------------------------------------------
-constexpr int DLT_LANES = 8;
 __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points, const int32_t* __restrict__ view_off,
                                                      const int32_t* __restrict__ view_cam,
                                                      const double* __restrict__ view_uv, double* xyz_out,
                                                      uint8_t* ok_out) {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = gid / DLT_LANES, sub = gid & (DLT_LANES - 1);
-    const bool live = i < n_points;           // whole groups are live or not; shuffles below are executed by every lane
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_points) return;
     double A[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-    if (live) {
-        const int k0 = __ldg(view_off + i), k1 = __ldg(view_off + i + 1);
-        for (int k = k0 + sub; k < k1; k += DLT_LANES) {
-            const int cam = __ldg(view_cam + k);
-            const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
-            double ccr[12];
-            {
-                const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
-                ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
-                ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
-            }
-            const double* in = P.intr + 10 * __ldg(P.cam_model + cam);
-            double intr[10];
+    const int k0 = __ldg(view_off + i), k1 = __ldg(view_off + i + 1);
+    int model = -1;
+    double intr[10];
+    int cam_next = k0 < k1 ? __ldg(view_cam + k0) : 0;
+    for (int k = k0; k < k1; k++) {
+        const int cam = cam_next;
+        if (k + 1 < k1) cam_next = __ldg(view_cam + k + 1);   // next index in flight during this view's gathers
+        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+        double ccr[12];
+        {
+            const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
+            ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
+            ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
+        }
+        const int m = __ldg(P.cam_model + cam);
+        if (m != model) {
+            model = m;
+            const double* in = P.intr + 10 * m;
 #pragma unroll
             for (int j = 0; j < 5; j++) { const double2 v = ldg2(in + 2 * j); intr[2 * j] = v.x; intr[2 * j + 1] = v.y; }
-            const double2 uv = ldg2(view_uv + 2 * (size_t)k);
-            double d[3];
-            dir_from_uv(uv.x, uv.y, intr, d);
-            dlt_accumulate(ccr, d, A, b);
         }
+        const double2 uv = ldg2(view_uv + 2 * (size_t)k);
+        double d[3];
+        dir_from_uv(uv.x, uv.y, intr, d);
+        dlt_accumulate(ccr, d, A, b);
     }
-#pragma unroll
-    for (int o = DLT_LANES / 2; o > 0; o >>= 1) {
-#pragma unroll
-        for (int j = 0; j < 6; j++) A[j] += __shfl_xor_sync(FULL, A[j], o);
-#pragma unroll
-        for (int j = 0; j < 3; j++) b[j] += __shfl_xor_sync(FULL, b[j], o);
-    }
-    if (!live || sub != 0) return;
     double Ai[6];
     const bool ok = inv3_sym(A, Ai);
     double x0 = 0.0, x1 = 0.0, x2 = 0.0;
@@ -263,10 +258,7 @@ __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points,
 }
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st) {
-    if (n_points) {
-        const long long threads = (long long)n_points * DLT_LANES;
-        k_triangulate<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
-    }
+    if (n_points) k_triangulate<<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
 }
 
 }  // namespace sba
