@@ -473,7 +473,7 @@ def run_b200(a):
     if rank == 0 and world == 1 and not a.no_cpu_baseline and not a.free_intrinsics and not a.mixed:
         # bounded sample: 3 LM iterations of the full scene (the parity tests' count), no warm-up; the cost history is held
         # against the GPU's below
-        cpu = cpu_leg(a.shape, 3, 0, a.pcg_tol, a.pcg_max_iters, scene=scene, budget_s=60.0)
+        cpu = cpu_leg(a.shape, 3 if scene["n_obs"] < 10_000_000 else 1, 0, a.pcg_tol, a.pcg_max_iters, scene=scene, budget_s=60.0)
         gh = first_history
         ch = cpu["cost_history_first_solve"]
         m = min(len(gh), len(ch))
