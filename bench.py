@@ -399,7 +399,8 @@ def run_b200(a):
             kern["k_explicit_matvec"]["note"] = "stand-alone tile mat-vec kernel (operator hook / fallback), not launched by the PCG"
             share = {"k_pcg_solve": ms, "explicit_build": kern["explicit_build"]["ms"], "k_residual_jacobian": kern["k_residual_jacobian"]["ms"]}
     else:
-        share = {k: (pcg_per_step if k != "k_residual_jacobian" else 1.0) * v["ms"] for k, v in kern.items()}
+        # implicit operator: the two passes run once per CG iteration, everything else once per linearisation / LM iteration
+        share = {k: (pcg_per_step if k in ("k_camera_pass", "k_point_pass") else 1.0) * v["ms"] for k, v in kern.items()}
     dom = max(share, key=share.get)
     traffic = None
     traffic_source = None

@@ -125,22 +125,40 @@ __global__ void __launch_bounds__(DB) k_potrf_block(double* __restrict__ D, int 
 }
 
 // in-place dense Cholesky, lower factor; Linv_all: (n / 64) inverse diagonal blocks; work: n x 64 panel scratch.  Returns launches.
+// Two levels of blocking: 64-wide block columns are factorised and applied INSIDE a 256-wide panel only; the matrix behind the
+// panel is updated once per panel with K = 256 (a quarter of the big-GEMM launches, four times the arithmetic per C tile).
 int dense_cholesky(double* D, int n, double* Linv_all, double* work, int* flag, cudaStream_t st) {
     const int NB = n / DB;
+    constexpr int PW = 4;   // blocks per panel
     int launches = 0;
-    for (int kb = 0; kb < NB; kb++) {
-        const int k0 = DB * kb, rem = NB - kb - 1;
-        double* Li = Linv_all + (size_t)kb * DB * DB;
-        k_potrf_block<<<1, DB, 0, st>>>(D, n, k0, Li, flag);
-        launches++;
-        if (!rem) break;
-        double* A21 = D + (size_t)(k0 + DB) * n + k0;
-        // panel: L21 = A21 Linv^T (through the scratch panel: the GEMM is not in place)
-        k_dgemm<false, true><<<dim3(1, rem), 256, 0, st>>>(A21, n, Li, DB, work, DB, DB, 1.0, 0.0, 0);
-        cudaMemcpy2DAsync(A21, (size_t)n * sizeof(double), work, DB * sizeof(double), DB * sizeof(double), (size_t)rem * DB, cudaMemcpyDeviceToDevice, st);
-        // trailing update, lower tiles: A22 -= L21 L21^T
-        k_dgemm<false, true><<<dim3(rem, rem), 256, 0, st>>>(A21, n, A21, n, D + (size_t)(k0 + DB) * n + k0 + DB, n, DB, -1.0, 1.0, 2);
-        launches += 3;
+    for (int pb = 0; pb < NB; pb += PW) {
+        const int pe = std::min(NB, pb + PW);   // panel = block columns pb .. pe-1
+        for (int kb = pb; kb < pe; kb++) {
+            const int k0 = DB * kb, rem = NB - kb - 1;
+            double* Li = Linv_all + (size_t)kb * DB * DB;
+            k_potrf_block<<<1, DB, 0, st>>>(D, n, k0, Li, flag);
+            launches++;
+            if (!rem) break;
+            double* A21 = D + (size_t)(k0 + DB) * n + k0;
+            // L21 = A21 Linv^T for every row below (through the scratch panel: the GEMM is not in place)
+            k_dgemm<false, true><<<dim3(1, rem), 256, 0, st>>>(A21, n, Li, DB, work, DB, DB, 1.0, 0.0, 0);
+            cudaMemcpy2DAsync(A21, (size_t)n * sizeof(double), work, DB * sizeof(double), DB * sizeof(double), (size_t)rem * DB, cudaMemcpyDeviceToDevice, st);
+            launches += 2;
+            // update of the remaining block columns of THIS panel: A[k+1.., k+1..pe) -= L21 L21[0 .. pe-k-1)^T  (rows: all below;
+            // tiles above the diagonal are written too -- never read)
+            const int pc = pe - kb - 1;
+            if (pc > 0) {
+                k_dgemm<false, true><<<dim3(pc, rem), 256, 0, st>>>(A21, n, A21, n, D + (size_t)(k0 + DB) * n + k0 + DB, n, DB, -1.0, 1.0, 0);
+                launches++;
+            }
+        }
+        // everything behind the panel: A22 -= L_panel L_panel^T, K = panel width, lower tiles only
+        const int rem = NB - pe;
+        if (rem > 0) {
+            const double* Lp = D + (size_t)(DB * pe) * n + DB * pb;
+            k_dgemm<false, true><<<dim3(rem, rem), 256, 0, st>>>(Lp, n, Lp, n, D + (size_t)(DB * pe) * n + DB * pe, n, DB * (pe - pb), -1.0, 1.0, 2);
+            launches++;
+        }
     }
     return launches;
 }
