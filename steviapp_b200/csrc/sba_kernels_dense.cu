@@ -92,36 +92,46 @@ __global__ void __launch_bounds__(256) k_dgemm(const double* __restrict__ A, int
         }
 }
 
-// one CTA: Cholesky of the 64x64 diagonal block at D[k0, k0] in shared memory (lower factor written back, upper part zeroed)
-// and the inverse of the factor into Linv (64x64 row-major, lower triangular).  flag set when a pivot is not positive.
-__global__ void __launch_bounds__(DB) k_potrf_block(double* __restrict__ D, int n, int k0, double* __restrict__ Linv, int* flag) {
-    __shared__ double L[DB][DB + 1];
+// one CTA (256 threads): Cholesky of the 64x64 diagonal block at D[k0, k0] in shared memory (lower factor written back, upper part
+// zeroed) and the inverse of the factor into Linv (64x64 row-major, lower triangular).  flag set when a pivot is not positive.
+__global__ void __launch_bounds__(256) k_potrf_block(double* __restrict__ D, int n, int k0, double* __restrict__ Linv, int* flag) {
+    extern __shared__ double potrf_smem[];   // two 64 x 65 arrays (66.5 KB: dynamic)
+    double (*L)[DB + 1] = reinterpret_cast<double (*)[DB + 1]>(potrf_smem);
+    double (*X)[DB + 1] = reinterpret_cast<double (*)[DB + 1]>(potrf_smem + DB * (DB + 1));
     __shared__ int bad;
-    const int t = threadIdx.x;
-    if (t == 0) bad = 0;
-    for (int r = 0; r < DB; r++) L[r][t] = D[(size_t)(k0 + r) * n + k0 + t];
+    const int tid = threadIdx.x;
+    if (tid == 0) bad = 0;
+    for (int e = tid; e < DB * DB; e += 256) { const int r = e >> 6, c = e & 63; L[r][c] = D[(size_t)(k0 + r) * n + k0 + c]; }
     __syncthreads();
     for (int j = 0; j < DB; j++) {
-        if (t == 0) {
+        if (tid == 0) {
             const double d = L[j][j];
             if (!(d > 0.0)) { bad = 1; L[j][j] = 1.0; } else L[j][j] = sqrt(d);
         }
         __syncthreads();
-        if (t > j) L[t][j] /= L[j][j];
+        if (tid > j && tid < DB) L[tid][j] /= L[j][j];
         __syncthreads();
-        if (t > j) for (int c = j + 1; c <= t; c++) L[t][c] -= L[t][j] * L[c][j];   // row t of the trailing lower triangle
+        // trailing lower triangle (rows r > j, columns j < c <= r), elements dealt round-robin to the 256 threads
+        const int m = DB - 1 - j;
+        for (int e = tid; e < m * m; e += 256) {
+            const int r = j + 1 + e / m, c = j + 1 + e % m;
+            if (c <= r) L[r][c] -= L[r][j] * L[c][j];
+        }
         __syncthreads();
     }
-    for (int r = 0; r < DB; r++) D[(size_t)(k0 + r) * n + k0 + t] = t <= r ? L[r][t] : 0.0;
-    // inverse: thread t solves L x = e_t (column t of L^-1)
-    double x[DB];
-    for (int i = 0; i < DB; i++) {
-        double s = i == t ? 1.0 : 0.0;
-        for (int k = t; k < i; k++) s -= L[i][k] * x[k];
-        x[i] = i < t ? 0.0 : s / L[i][i];
+    for (int e = tid; e < DB * DB; e += 256) { const int r = e >> 6, c = e & 63; D[(size_t)(k0 + r) * n + k0 + c] = c <= r ? L[r][c] : 0.0; }
+    // inverse: thread t < 64 solves L x = e_t (column t of L^-1) by forward substitution, X in shared memory
+    if (tid < DB) {
+        const int t = tid;
+        for (int i = 0; i < DB; i++) {
+            double sacc = i == t ? 1.0 : 0.0;
+            for (int k = t; k < i; k++) sacc -= L[i][k] * X[k][t];
+            X[i][t] = i < t ? 0.0 : sacc / L[i][i];
+        }
     }
-    for (int i = 0; i < DB; i++) Linv[(size_t)i * DB + t] = x[i];
-    if (t == 0 && bad) *flag = 1;
+    __syncthreads();
+    for (int e = tid; e < DB * DB; e += 256) { const int r = e >> 6, c = e & 63; Linv[(size_t)r * DB + c] = X[r][c]; }
+    if (tid == 0 && bad) *flag = 1;
 }
 
 // in-place dense Cholesky, lower factor; Linv_all: (n / 64) inverse diagonal blocks; work: n x 64 panel scratch.  Returns launches.
@@ -130,13 +140,16 @@ __global__ void __launch_bounds__(DB) k_potrf_block(double* __restrict__ D, int 
 int dense_cholesky(double* D, int n, double* Linv_all, double* work, int* flag, cudaStream_t st) {
     const int NB = n / DB;
     constexpr int PW = 4;   // blocks per panel
+    constexpr size_t POTRF_SMEM = 2 * DB * (DB + 1) * sizeof(double);
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(k_potrf_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)POTRF_SMEM); attr_set = true; }
     int launches = 0;
     for (int pb = 0; pb < NB; pb += PW) {
         const int pe = std::min(NB, pb + PW);   // panel = block columns pb .. pe-1
         for (int kb = pb; kb < pe; kb++) {
             const int k0 = DB * kb, rem = NB - kb - 1;
             double* Li = Linv_all + (size_t)kb * DB * DB;
-            k_potrf_block<<<1, DB, 0, st>>>(D, n, k0, Li, flag);
+            k_potrf_block<<<1, 256, POTRF_SMEM, st>>>(D, n, k0, Li, flag);
             launches++;
             if (!rem) break;
             double* A21 = D + (size_t)(k0 + DB) * n + k0;
@@ -163,28 +176,49 @@ int dense_cholesky(double* D, int n, double* Linv_all, double* work, int* flag, 
     return launches;
 }
 
-// x = S^-1 b with the factor: forward and backward substitution by blocks (one small CTA per block step)
-__global__ void __launch_bounds__(4 * DB) k_trsv_block(const double* __restrict__ L, int n, const double* __restrict__ Linv_all, double* x, int kb, int backward) {
-    __shared__ double s[DB], part[4][DB];
-    const int t = threadIdx.x & (DB - 1), h = threadIdx.x / DB, k0 = DB * kb;   // four threads per row split the sum, folded in fixed order
-    double acc = 0.0;
-    if (!backward) { for (int j = h; j < k0; j += 4) acc += L[(size_t)(k0 + t) * n + j] * x[j]; }
-    else { for (int j = k0 + DB + h; j < n; j += 4) acc += L[(size_t)j * n + k0 + t] * x[j]; }
-    part[h][t] = acc;
+// x = S^-1 b with the factor, right-looking by 64-row blocks.  One launch per block step: EVERY CTA recomputes the block's
+// solution x_k = inv(L_kk) b_k (forward) / inv(L_kk)^T b_k (backward) from the by-then final b_k (a 64x64 product), CTA 0 stores it,
+// and the other CTAs subtract its contribution from their share of the rest of the right-hand side:
+//   forward:  b[r] -= L[r, k-block] . x_k   for rows r behind the block (each CTA 64 rows, row segments of 512 B);
+//   backward: b[c] -= L[k-block, c]^T x_k   for columns c in front of the block (each CTA 256 columns, coalesced along c).
+// n^2 / 2 matrix elements are read once, by many CTAs, instead of by one.
+__global__ void __launch_bounds__(256) k_trsv_step(const double* __restrict__ L, int n, const double* __restrict__ Linv_all, double* x, int kb, int backward) {
+    __shared__ double bk[DB], xk[DB];
+    const int tid = threadIdx.x, k0 = DB * kb;
+    if (tid < DB) bk[tid] = x[k0 + tid];
     __syncthreads();
-    if (h == 0) s[t] = x[k0 + t] - ((part[0][t] + part[1][t]) + (part[2][t] + part[3][t]));
-    __syncthreads();
-    if (h != 0) return;
     const double* Li = Linv_all + (size_t)kb * DB * DB;
-    double v = 0.0;
-    if (!backward) { for (int j = 0; j <= t; j++) v += Li[(size_t)t * DB + j] * s[j]; }
-    else { for (int j = t; j < DB; j++) v += Li[(size_t)j * DB + t] * s[j]; }
-    x[k0 + t] = v;
+    if (tid < DB) {
+        double v = 0.0;
+        if (!backward) { for (int j = 0; j <= tid; j++) v += Li[(size_t)tid * DB + j] * bk[j]; }
+        else { for (int j = tid; j < DB; j++) v += Li[(size_t)j * DB + tid] * bk[j]; }
+        xk[tid] = v;
+    }
+    __syncthreads();
+    if (blockIdx.x == 0) { if (tid < DB) x[k0 + tid] = xk[tid]; return; }
+    const int w = blockIdx.x - 1;
+    if (!backward) {
+        // 64 rows per CTA, four threads per row (16 columns each), folded in fixed order
+        __shared__ double part[4][DB];
+        const int r = k0 + DB + DB * w + (tid & 63), h = tid >> 6;
+        double acc = 0.0;
+        if (r < n) { const double* row = L + (size_t)r * n + k0 + 16 * h; for (int c = 0; c < 16; c++) acc += row[c] * xk[16 * h + c]; }
+        part[h][tid & 63] = acc;
+        __syncthreads();
+        if (h == 0 && r < n) x[r] -= (part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid]);
+    } else {
+        const int c = 256 * w + tid;
+        if (c < k0) {
+            double acc = 0.0;
+            for (int r = 0; r < DB; r++) acc += L[(size_t)(k0 + r) * n + c] * xk[r];
+            x[c] -= acc;
+        }
+    }
 }
 int dense_solve(const double* L, int n, const double* Linv_all, double* x, cudaStream_t st) {
     const int NB = n / DB;
-    for (int kb = 0; kb < NB; kb++) k_trsv_block<<<1, 4 * DB, 0, st>>>(L, n, Linv_all, x, kb, 0);
-    for (int kb = NB - 1; kb >= 0; kb--) k_trsv_block<<<1, 4 * DB, 0, st>>>(L, n, Linv_all, x, kb, 1);
+    for (int kb = 0; kb < NB; kb++) k_trsv_step<<<1 + (NB - 1 - kb), 256, 0, st>>>(L, n, Linv_all, x, kb, 0);
+    for (int kb = NB - 1; kb >= 0; kb--) k_trsv_step<<<1 + (DB * kb + 255) / 256, 256, 0, st>>>(L, n, Linv_all, x, kb, 1);
     return 2 * NB;
 }
 
