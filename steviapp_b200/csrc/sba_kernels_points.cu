@@ -59,28 +59,21 @@ __device__ __forceinline__ void store_point_blocks(const DevProblem& P, int pt, 
         st2(gp, v[6], v[7]); st2(gp + 2, v[8], 0.0);
     }
 }
-__global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;   // Nq is a multiple of 32: whole warps in range
-    if (q >= P.Nq) return;
-    const int lane = threadIdx.x & 31;
+// one q slot; `crec(cam, ccr)` fetches Rt (9) and t (3) of the camera (global gather or shared-memory table)
+template <class Fetch>
+__device__ __forceinline__ void linearize_slot(const DevProblem& P, int q, int lane, Fetch crec) {
     const int pt = __ldcs(P.q_pt + q);
     double v[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (pt >= 0) {   // padding: planes stay zero
         const int cam = __ldcs(P.q_cam + q);
         const d4 Xp = ld256(P.pts + 4 * (size_t)pt);
         const double X[3] = {Xp.x, Xp.y, Xp.z};
-        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
-        // only Rt and t are needed (C is not kept in point order: its expressions, hence Jr, are dead code here):
-        // three 256-bit gathers instead of eleven 128-bit ones
+        // only Rt and t are needed (C is not kept in point order: its expressions, hence Jr, are dead code here)
         double ccr[22];
-        {
-            const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
-            ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
-            ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
+        crec(cam, ccr);
 #pragma unroll
-            for (int i = 12; i < 22; i++) ccr[i] = 0.0;
-        }
-        const double* in = P.intr + 10 * __ldg(P.cam_model + cam);
+        for (int i = 12; i < 22; i++) ccr[i] = 0.0;
+        const double* in = P.intr + 10 * (P.Nm == 1 ? 0 : __ldg(P.cam_model + cam));
         double intr[10];
 #pragma unroll
         for (int i = 0; i < 5; i++) { const double2 t = ldg2(in + 2 * i); intr[2 * i] = t.x; intr[2 * i + 1] = t.y; }
@@ -122,6 +115,34 @@ __global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
         }
     }
 }
+// variant G: three 256-bit gathers of the camera record per slot (any camera count)
+__global__ void __launch_bounds__(256) k_linearize_q(DevProblem P) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;   // Nq is a multiple of 32: whole warps in range
+    if (q >= P.Nq) return;
+    linearize_slot(P, q, threadIdx.x & 31, [&](int cam, double* ccr) {
+        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
+        const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
+        ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
+        ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
+    });
+}
+// variant S: the whole table {Rt, t} (96 B per camera) staged in shared memory by persistent blocks (one per SM): the
+// per-slot gather becomes six LDS.128 instead of 96 L1 wavefronts per warp -- the kernel is bound by the L1 / MIO wavefront
+// rate of its gathers, not by HBM bytes.  Used when 96 * Nc fits the SM's shared memory (Venice: 171 KB).
+__global__ void __launch_bounds__(1024, 1) k_linearize_q_s(DevProblem P) {
+    extern __shared__ double2 s_cr[];   // 6 double2 per camera
+    for (int i = threadIdx.x; i < 6 * P.Nc; i += blockDim.x) {
+        const int c = i / 6, j = i - 6 * c;
+        s_cr[i] = *reinterpret_cast<const double2*>(P.cam_cache + (size_t)CAM_CACHE_STRIDE * c + 2 * j);
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < P.Nq; q += gridDim.x * blockDim.x)   // Nq % 32 == 0: whole warps
+        linearize_slot(P, q, lane, [&](int cam, double* ccr) {
+#pragma unroll
+            for (int j = 0; j < 6; j++) { const double2 t = s_cr[6 * cam + j]; ccr[2 * j] = t.x; ccr[2 * j + 1] = t.y; }
+        });
+}
 __global__ void k_point_blocks_heavy(DevProblem P) {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= P.Nh) return;
@@ -133,7 +154,19 @@ __global__ void k_point_blocks_heavy(DevProblem P) {
 }
 void launch_linearize_points(const DevProblem& P, cudaStream_t st) {
     if (P.Nq == 0) return;
-    k_linearize_q<<<cdiv(P.Nq, 256), 256, 0, st>>>(P);
+    static int sms = 0, smem_max = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        cudaFuncSetAttribute(k_linearize_q_s, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+    }
+    const size_t table = 96 * (size_t)P.Nc;
+    if (P.pp_variant != 1 && table <= (size_t)smem_max && P.Nq >= 256 * 1024)
+        k_linearize_q_s<<<std::min(sms, cdiv(P.Nq, 1024)), 1024, table, st>>>(P);
+    else
+        k_linearize_q<<<cdiv(P.Nq, 256), 256, 0, st>>>(P);
     if (P.Nh) k_point_blocks_heavy<<<cdiv(P.Nh, 128), 128, 0, st>>>(P);
 }
 
