@@ -350,6 +350,12 @@ int sba_bal_raw(const sba_bal* b, int32_t* cam_idx, int32_t* pt_idx, double* xy,
  * n_undistort_failed (may be NULL) counts observations whose radius equation did not converge (kept distorted). */
 int sba_bal_convert(const sba_bal* b, double* raxis, double* t, double* intr10, int32_t* cam_model, double* xyz,
                     int32_t* cam_idx, int32_t* pt_idx, double* uv, int32_t* n_undistort_failed);
+/* the file's OWN objective, 1/2 sum |pixel(cam9, xyz) - xy|^2 with the BAL projection (bal_example.cpp:168-204) and its RMS in
+ * pixels, for cameras cam9 / points xyz (NULL = the file's): costs in BAL's metric before / after a solve.  The engine
+ * minimises the residual with the distortion moved to the measurement (first-order equivalent, see sba_bal_convert). */
+int sba_bal_cost(const sba_bal* b, const double* cam9, const double* xyz, double* cost, double* rms_px);
+/* engine-convention poses (after a solve) back to BAL cameras, f / k1 / k2 from the file */
+int sba_bal_cameras_from_engine(const sba_bal* b, const double* raxis, const double* t, double* cam9_out);
 /* writes a BAL file (%.17g: reading it back reproduces every double) */
 int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs, const int32_t* cam_idx, const int32_t* pt_idx,
                   const double* xy, const double* cam9, const double* xyz);

@@ -25,7 +25,7 @@ EXPORTS = [
     "sba_evaluate_intrinsics_jacobian", "sba_evaluate_offset", "sba_normal_blocks", "sba_schur_matvec", "sba_solve", "sba_set_iteration_callback", "sba_set_options",
     "sba_time_stage", "sba_triangulate", "sba_comm_unique_id", "sba_comm_init", "sba_partition_points",
     "sba_problem_sizes", "sba_explicit_info", "sba_explicit_shard", "sba_explicit_sparse_info", "sba_explicit_tiles", "sba_version",
-    "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write",
+    "sba_bal_open", "sba_bal_close", "sba_bal_error", "sba_bal_sizes", "sba_bal_raw", "sba_bal_convert", "sba_bal_write", "sba_bal_cost", "sba_bal_cameras_from_engine",
     "sba_pushbroom_equivalent_uv",
     "sba_set_intrinsics_blocks", "sba_add_intrinsics_priors", "sba_set_sensor_offsets", "sba_set_lever_arms", "sba_shared_info",
     "sba_point_covariances", "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
@@ -132,6 +132,8 @@ def load():
     lib.sba_bal_sizes.argtypes = [vp, vp, vp, vp]
     lib.sba_bal_raw.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.sba_bal_convert.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.sba_bal_cost.argtypes = [vp, vp, vp, P(dbl), P(dbl)]
+    lib.sba_bal_cameras_from_engine.argtypes = [vp, vp, vp, vp]
     lib.sba_pushbroom_equivalent_uv.argtypes = [C.c_int32, vp, C.c_double, C.c_double, C.c_double, vp, vp, vp, vp]
     lib.sba_bal_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]
     for name in EXPORTS:

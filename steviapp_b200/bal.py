@@ -7,6 +7,7 @@ registers on an `SBASolver`.
 """
 import ctypes as C
 import os
+import warnings
 
 import numpy as np
 
@@ -63,6 +64,9 @@ def load_bal(path, fix_first_camera=True):
                                    C.byref(failed)), "sba_bal_convert")
     finally:
         lib.sba_bal_close(h)
+    if failed.value:
+        warnings.warn(f"{path}: the radial distortion of {failed.value} of {no} observations could not be removed (no root of the radius "
+                      "equation: wide-angle pixels beyond the turning point of the polynomial); they are kept distorted", RuntimeWarning)
     cam_fixed = np.zeros(nc, np.uint8)
     if fix_first_camera:
         cam_fixed[0] = 1
@@ -74,6 +78,27 @@ def load_bal(path, fix_first_camera=True):
         "prior_kind": np.zeros(0, np.int32), "prior_index": np.zeros(0, np.int32),
         "prior_A": np.zeros((0, 9)), "prior_b": np.zeros((0, 3)),
     }
+
+
+def bal_cost(path, raxis=None, t=None, pts=None):
+    """Cost and RMS (pixels) of a BAL file in BAL's OWN metric (1/2 sum |projection - xy|^2, bal_example.cpp:168-204), for the
+    file's parameters or -- raxis / t / pts given, in the engine's conventions as load_bal returns and a solve updates them --
+    for a solution: the figure to quote against published BAL numbers (the engine's own cost is first-order equivalent only)."""
+    lib = _capi.load()
+    h = C.c_void_p()
+    _check(lib.sba_bal_open(os.fsencode(path), C.byref(h)), "sba_bal_open")
+    try:
+        cam9 = None
+        if raxis is not None:
+            raxis = np.ascontiguousarray(raxis, np.float64); t = np.ascontiguousarray(t, np.float64)
+            cam9 = np.empty((raxis.shape[0], 9))
+            _check(lib.sba_bal_cameras_from_engine(h, _ptr(raxis), _ptr(t), _ptr(cam9)), "sba_bal_cameras_from_engine")
+        xyz = None if pts is None else np.ascontiguousarray(pts, np.float64)
+        cost, rms = C.c_double(), C.c_double()
+        _check(lib.sba_bal_cost(h, None if cam9 is None else _ptr(cam9), None if xyz is None else _ptr(xyz), C.byref(cost), C.byref(rms)), "sba_bal_cost")
+        return cost.value, rms.value
+    finally:
+        lib.sba_bal_close(h)
 
 
 def write_bal(path, cam_idx, pt_idx, xy, cam9, xyz):

@@ -210,6 +210,49 @@ int sba_bal_convert(const sba_bal* b, double* raxis, double* t, double* intr10, 
     return SBA_OK;
 }
 
+// The file's OWN objective (bal_example.cpp:168-204): 1/2 sum |f (1 + k1 |p|^2 + k2 |p|^4) p - xy|^2, p = -P.xy / P.z,
+// P = R(r) X + t -- so that costs before / after a solve can be quoted in BAL's metric (the engine minimises the residual
+// with the distortion moved to the measurement, which is only first-order equivalent).  cam9 / xyz: NULL = the file's.
+int sba_bal_cost(const sba_bal* b, const double* cam9, const double* xyz, double* cost, double* rms_px) {
+    if (!b) return bal_fail("sba_bal_cost: null handle");
+    if (!cam9) cam9 = b->cam9.data();
+    if (!xyz) xyz = b->xyz.data();
+    double sum = 0.0;
+    for (int32_t i = 0; i < b->n_obs; i++) {
+        const double* c9 = cam9 + 9 * (size_t)b->cam[(size_t)i];
+        const double* X = xyz + 3 * (size_t)b->pt[(size_t)i];
+        double R[9];
+        rodrigues(c9, R);
+        const double Px = R[0] * X[0] + R[1] * X[1] + R[2] * X[2] + c9[3], Py = R[3] * X[0] + R[4] * X[1] + R[5] * X[2] + c9[4],
+                     Pz = R[6] * X[0] + R[7] * X[1] + R[8] * X[2] + c9[5];
+        const double px = -Px / Pz, py = -Py / Pz, r2 = px * px + py * py;
+        const double s = c9[6] * (1.0 + r2 * (c9[7] + c9[8] * r2));
+        const double ex = s * px - b->xy[2 * (size_t)i], ey = s * py - b->xy[2 * (size_t)i + 1];
+        sum += ex * ex + ey * ey;
+    }
+    if (cost) *cost = 0.5 * sum;
+    if (rms_px) *rms_px = b->n_obs ? std::sqrt(sum / (2.0 * b->n_obs)) : 0.0;
+    return SBA_OK;
+}
+
+// engine-convention poses (sba_bal_convert's raxis / t after a solve) back to BAL cameras: R = F R_e^T, t = -R t_e with
+// F = diag(1, -1, -1); f, k1, k2 are the file's (held constant by the conversion)
+int sba_bal_cameras_from_engine(const sba_bal* b, const double* raxis, const double* t, double* cam9_out) {
+    if (!b || !raxis || !t || !cam9_out) return bal_fail("sba_bal_cameras_from_engine: null argument");
+    for (int32_t i = 0; i < b->n_cams; i++) {
+        double Re[9], R[9];
+        rodrigues(raxis + 3 * (size_t)i, Re);
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) R[3 * r + c] = Re[3 * c + r] * (r == 0 ? 1.0 : -1.0);   // F R_e^T
+        double* o = cam9_out + 9 * (size_t)i;
+        log_rotation(R, o);
+        const double* te = t + 3 * (size_t)i;
+        for (int r = 0; r < 3; r++) o[3 + r] = -(R[3 * r] * te[0] + R[3 * r + 1] * te[1] + R[3 * r + 2] * te[2]);
+        o[6] = b->cam9[9 * (size_t)i + 6]; o[7] = b->cam9[9 * (size_t)i + 7]; o[8] = b->cam9[9 * (size_t)i + 8];
+    }
+    return SBA_OK;
+}
+
 int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs, const int32_t* cam_idx, const int32_t* pt_idx,
                   const double* xy, const double* cam9, const double* xyz) {
     if (!path || !cam_idx || !pt_idx || !xy || !cam9 || !xyz || n_cams <= 0 || n_pts <= 0 || n_obs < 0) return bal_fail("sba_bal_write: bad argument");

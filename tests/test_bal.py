@@ -107,6 +107,36 @@ def test_oracle_cost_is_zero_on_an_exact_bal_problem(tmp_path):
     assert ev["cost"] < 1e-16 * ci.shape[0] * 1e6, ev["cost"]
 
 
+def test_bal_cost_in_the_files_own_metric(tmp_path):
+    """sba_bal_cost = 1/2 sum |bal_project - xy|^2 (the numpy statement above), for the file's parameters and -- through
+    sba_bal_cameras_from_engine -- for engine-convention poses; the round trip file -> engine -> file reproduces the cameras."""
+    ci, pi, xy, cam9, xyz = make_bal(seed=5, noise=0.7)
+    path = tmp_path / "problem.txt"
+    bal.write_bal(path, ci, pi, xy, cam9, xyz)
+    want = 0.5 * sum(((bal_project(cam9[c], xyz[p])[0] - m) ** 2).sum() for c, p, m in zip(ci, pi, xy))
+    cost, rms = bal.bal_cost(path)
+    assert abs(cost - want) <= 1e-12 * want and abs(rms - np.sqrt(2 * want / (2 * ci.size))) <= 1e-12 * rms
+    sc = bal.load_bal(path)
+    cost2, _ = bal.bal_cost(path, sc["raxis"], sc["t"], sc["pts"])          # engine conventions back to BAL cameras
+    assert abs(cost2 - want) <= 1e-10 * want
+    moved = sc["pts"] + 0.01
+    cost3, _ = bal.bal_cost(path, sc["raxis"], sc["t"], moved)
+    want3 = 0.5 * sum(((bal_project(cam9[c], xyz[p] + 0.01)[0] - m) ** 2).sum() for c, p, m in zip(ci, pi, xy))
+    assert abs(cost3 - want3) <= 1e-10 * want3
+
+
+def test_undistortion_failures_are_surfaced(tmp_path):
+    """A wide-angle pixel beyond the turning point of 1 + k1 r^2 + k2 r^4 has no undistorted radius: counted AND warned about."""
+    ci, pi, xy, cam9, xyz = make_bal(seed=3)
+    cam9[:, 7] = -0.6; cam9[:, 8] = 0.0
+    xy = xy.copy(); xy[0] = cam9[ci[0], 6] * np.array([2.0, 2.0])           # normalised radius 2.8: past the maximum of r (1 - 0.6 r^2)
+    path = tmp_path / "problem.txt"
+    bal.write_bal(path, ci, pi, xy, cam9, xyz)
+    with pytest.warns(RuntimeWarning, match="could not be removed"):
+        sc = bal.load_bal(path)
+    assert sc["undistort_failed"] >= 1
+
+
 def test_loaded_problem_shards_by_points(tmp_path):
     """SURVEY 8(e) sharding applies to a loaded file as to the synthetic scenes: contiguous point ranges, every observation
     on exactly one rank, cameras replicated."""
