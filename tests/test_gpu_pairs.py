@@ -5,7 +5,7 @@ import pytest
 
 from conftest import relerr
 from steviapp_b200 import SBASolver, synthetic
-from test_pairs_host import image_pair_scene, pair_scene
+from test_pairs_host import cross_projector_scene, image_pair_scene, pair_scene
 
 pytestmark = pytest.mark.gpu
 
@@ -22,6 +22,14 @@ def gpu(sc, **opts):
 def test_reference_known_answer_image_pair():
     # tests/test_sba_solver/main.cpp:335-492: the factor graph of two images and five correspondences costs < 1e-6 at the truth
     s, _ = gpu(image_pair_scene())
+    e = s.evaluate(residuals=False, jacobians=False)
+    r, j = s.evaluate_pairs()
+    assert abs(e["cost"]) < 1e-6 and np.abs(r).max() < 1e-9
+
+
+def test_reference_known_answer_cross_projector(sba_lib):
+    # tests/test_uv_projectors/main.cpp:258-382: frame camera x push-broom camera, cost < 1e-6 at the truth
+    s, _ = gpu(cross_projector_scene(sba_lib))
     e = s.evaluate(residuals=False, jacobians=False)
     r, j = s.evaluate_pairs()
     assert abs(e["cost"]) < 1e-6 and np.abs(r).max() < 1e-9

@@ -1,7 +1,8 @@
 """UV <-> UV cross-projection cost without a GPU: the product's functor on its own forward-mode duals
 (steviapp_b200/csrc/sba_jet.cuh, compiled for the host by tests/hostmath) against the oracle's restatement of UV2UVCost
 (costfunctors/modularuvprojection.h:660-795), and the oracle against the reference's imagePair known-answer vector
-(tests/test_sba_solver/main.cpp:335-492: cost < 1e-6 at the exact solution)."""
+(tests/test_sba_solver/main.cpp:335-492: cost < 1e-6 at the exact solution) and the frame / push-broom cross-projector vector
+(tests/test_uv_projectors/main.cpp:258-382)."""
 import ctypes as C
 
 import numpy as np
@@ -53,6 +54,31 @@ def pair_scene(shape="small", n_pairs=400, seed=3, noise=0.5, outliers=0.0):
 
 def test_oracle_image_pair_known_answer(oracle):
     e = oracle.ExtProblem(image_pair_scene()).evaluate()
+    assert abs(e["cost"]) < 1e-6 and np.abs(e["pair_residuals"]).max() < 1e-9
+
+
+def cross_projector_scene(sba_lib):
+    """tests/test_uv_projectors/main.cpp:258-382 (testCrossUVProjector): a frame camera (f = 35, pp at the image centre, at
+    (27, -33, 0)) and a push-broom camera (f = 35, pp = 320, sensor width 640, at the origin, zero polynomials) see the point
+    (42, 0, 35); the cross-projection cost is < 1e-6.  The push-broom pixel enters through sba_pushbroom_equivalent_uv."""
+    f, ppx, ppy, pbpp = 35.0, 320.0, 240.0, 320.0          # the frame camera's pp cancels out of the vector (pixel = offset + pp)
+    X = np.array([42.0, 0.0, f]); t_ph = np.array([27.0, -33.0, 0.0])
+    uv_ph = (np.array([X[0] - t_ph[0] + ppx, X[1] - t_ph[1] + ppy]) / X[2]) * f        # main.cpp:336-339
+    uv_pb = (np.array([[X[0] + pbpp, X[1]]]) / X[2]) * f                                # main.cpp:341-344
+    zero6 = np.zeros(6); uv_eq = np.empty((1, 2)); intr_pb = np.empty(10)
+    assert sba_lib.sba_pushbroom_equivalent_uv(1, ptr(np.ascontiguousarray(uv_pb)), 640.0, f, pbpp, ptr(zero6), ptr(zero6), ptr(uv_eq), ptr(intr_pb)) == 0
+    sc = image_pair_scene()
+    sc["intrinsics"] = np.array([[f, ppx, ppy, 0, 0, 0, 0, 0, 0, 0], intr_pb])
+    sc["cam_model"] = np.array([0, 1], np.int32)
+    sc["raxis"] = np.zeros((2, 3)); sc["t"] = np.array([t_ph, [0.0, 0.0, 0.0]])
+    sc["pair_cam"] = np.array([[0, 1]], np.int32)
+    sc["pair_uv"] = np.array([[uv_ph[0], uv_ph[1], uv_eq[0, 0], uv_eq[0, 1]]])
+    return sc
+
+
+def test_oracle_cross_projector_known_answer(oracle, sba_lib):
+    sc = cross_projector_scene(sba_lib)
+    e = oracle.ExtProblem(sc).evaluate()
     assert abs(e["cost"]) < 1e-6 and np.abs(e["pair_residuals"]).max() < 1e-9
 
 
