@@ -16,6 +16,7 @@ $NVCC $FLAGS -x cu -c sba_comm.cpp -o ../build/sba_comm.o & pids+=($!)
 $NVCC $FLAGS -x cu -c sba_capi.cpp -o ../build/sba_capi.o & pids+=($!)
 $NVCC $FLAGS -x cu -c sba_bal.cpp -o ../build/sba_bal.o & pids+=($!)
 $NVCC $FLAGS -x cu -c sba_projectors.cpp -o ../build/sba_projectors.o & pids+=($!)
+$NVCC $FLAGS -x cu -c sba_project.cpp -o ../build/sba_project.o & pids+=($!)
 for p in "${pids[@]}"; do wait $p; done
 $NVCC -shared -o $OUT ../build/*.o -ccbin $CXX_HOST -lcudart_static -ldl -lpthread -lrt
 echo "built $(readlink -f $OUT)"

@@ -368,6 +368,44 @@ int sba_bal_write(const char* path, int32_t n_cams, int32_t n_pts, int32_t n_obs
 int sba_pushbroom_equivalent_uv(int32_t n, const double* uv, double sensor_width, double f, double pp, const double* as6,
                                 const double* bs6, double* uv_out, double* intr10_out);
 
+/* ---- The reference's project files (".steviapproj").  Replaces Project::load / save
+ * (libs/datablocks/project.cpp:93-221) and the part of the SBA modules that turns data blocks into the problem:
+ * GenericSBAGraphReductor (sparsesolver/sbagraphreductor.cpp:172-194: items with fewer observations than degrees of
+ * freedom drop out, to the fixed point), LandmarksSBAModule::init (sbamodules/landmarkssbamodule.cpp:111-205),
+ * ModularSBASolver::getNodeForFrame (modularsbasolver.cpp:233-305), ImageAlignementSBAModule::init
+ * (sbamodules/imagealignementsbamodule.cpp:206-440), PinholeCamProjModule::init (pinholecameraprojectormodule.cpp:302-533),
+ * and the three writeResults (landmarkssbamodule.cpp:207-262, imagealignementsbamodule.cpp:446-490,
+ * pinholecameraprojectormodule.cpp:535-574).  Host code only: no CUDA device needed.
+ * Errors: SBA_ERR_INVALID with the text in sba_project_error() (unreadable file, malformed JSON, a landmark with a
+ * geographic CRS -- its conversion needs PROJ --, an image attached to a trajectory and a mounting).
+ * Engine indices: models = the Cameras some kept image uses (order of first use), images / landmarks in file order. */
+typedef struct sba_project sba_project;
+#define SBA_PROJECT_FIX_CAMERA_INTERNAL 1   /* FixedParameter::CameraInternal (fixedpreoptimizedparameters.h) */
+int sba_project_open(const char* path, sba_project** out);
+void sba_project_close(sba_project* p);
+const char* sba_project_error(void);
+/* any pointer may be NULL.  n_intrinsics_priors is the count with every intrinsic block free (an upper bound);
+ * n_images_without_camera counts enabled, constrained images that were left out because no Camera is assigned. */
+int sba_project_sizes(const sba_project* p, int32_t* n_models, int32_t* n_images, int32_t* n_landmarks, int32_t* n_obs,
+                      int32_t* n_priors, int32_t* n_intrinsics_priors, int32_t* n_images_without_camera);
+/* data-block ids ("id" in the file) of the engine's models / images / landmarks */
+int sba_project_ids(const sba_project* p, int64_t* model_id, int64_t* image_id, int64_t* landmark_id);
+/* The problem in the conventions of this header (any pointer may be NULL; the four prior arrays and the four
+ * intrinsics-prior arrays go together): intr10 [10 n_models] + model_fixed_mask [n_models] for sba_set_intrinsics_blocks,
+ * raxis / t [3 n_images] + cam_model + cam_fixed for sba_set_poses, pts [3 n_landmarks] + pt_fixed for sba_set_points,
+ * obs_* for sba_add_observations (obs_info [4 n_obs], diagonal), prior_* for sba_add_priors, ipr_* for
+ * sba_add_intrinsics_priors (*n_intrinsics_priors = how many were written).  fixed_flags: SBA_PROJECT_FIX_CAMERA_INTERNAL. */
+int sba_project_convert(const sba_project* p, int32_t fixed_flags, double* intr10, uint8_t* model_fixed_mask, double* raxis, double* t,
+                        int32_t* cam_model, uint8_t* cam_fixed, double* pts, uint8_t* pt_fixed, int32_t* obs_cam, int32_t* obs_pt,
+                        double* obs_uv, double* obs_info, int32_t* prior_kind, int32_t* prior_index, double* prior_A9, double* prior_b3,
+                        int32_t* ipr_model, int32_t* ipr_block, double* ipr_A9, double* ipr_b3, int32_t* n_intrinsics_priors);
+/* writeResults of the three modules into the loaded document: "op" / "or" of the free images, "op" of the landmarks, the
+ * optimised "o*" parameters of the free Cameras; every value passes through float, as the modules store it.  Any array NULL
+ * = that part is left alone (raxis and t go together). */
+int sba_project_write_results(sba_project* p, const double* raxis, const double* t, const double* pts, const double* intr10);
+/* Project::save: the document as indented JSON with sorted keys (what QJsonDocument::toJson writes) */
+int sba_project_save(const sba_project* p, const char* path);
+
 const char* sba_version(void);
 
 #ifdef __cplusplus

@@ -6,5 +6,6 @@ The product is libsba_b200.so (C ABI: include/sba_b200.h); this package is its h
 from .solver import SBASolver, SBAError, default_options, comm_unique_id, partition_points  # noqa: F401
 from . import synthetic  # noqa: F401
 from . import bal  # noqa: F401
+from . import project  # noqa: F401
 
-__all__ = ["SBASolver", "SBAError", "default_options", "comm_unique_id", "partition_points", "synthetic", "bal"]
+__all__ = ["SBASolver", "SBAError", "default_options", "comm_unique_id", "partition_points", "synthetic", "bal", "project"]

@@ -29,6 +29,8 @@ EXPORTS = [
     "sba_pushbroom_equivalent_uv",
     "sba_set_intrinsics_blocks", "sba_add_intrinsics_priors", "sba_set_sensor_offsets", "sba_set_lever_arms", "sba_shared_info",
     "sba_point_covariances", "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
+    "sba_project_open", "sba_project_close", "sba_project_error", "sba_project_sizes", "sba_project_ids", "sba_project_convert",
+    "sba_project_write_results", "sba_project_save",
 ]
 
 
@@ -136,6 +138,15 @@ def load():
     lib.sba_bal_cameras_from_engine.argtypes = [vp, vp, vp, vp]
     lib.sba_pushbroom_equivalent_uv.argtypes = [C.c_int32, vp, C.c_double, C.c_double, C.c_double, vp, vp, vp, vp]
     lib.sba_bal_write.argtypes = [C.c_char_p, C.c_int32, C.c_int32, C.c_int32, vp, vp, vp, vp, vp]
+    lib.sba_project_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+    lib.sba_project_close.argtypes = [vp]
+    lib.sba_project_close.restype = None
+    lib.sba_project_error.restype = C.c_char_p
+    lib.sba_project_sizes.argtypes = [vp] + [P(i32)] * 7
+    lib.sba_project_ids.argtypes = [vp, vp, vp, vp]
+    lib.sba_project_convert.argtypes = [vp, i32] + [vp] * 20 + [P(i32)]
+    lib.sba_project_write_results.argtypes = [vp, vp, vp, vp, vp]
+    lib.sba_project_save.argtypes = [vp, C.c_char_p]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int:   # default restype: all status-returning functions
