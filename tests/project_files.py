@@ -82,3 +82,28 @@ def write(path, landmarks, images, cameras, local_transform=None, extra=None):
     with open(path, "w") as f:
         json.dump(doc, f, indent=4)
     return doc
+
+
+def from_scene(path, sc, intr_sigma=None, obs_sigma=None, gcp_sigma=0.01, n_gcp=4, pose_sigma=None):
+    """A project file that states a synthetic scene (steviapp_b200.synthetic.make_scene): one Camera per intrinsics model,
+    images with their initial poses as optimised values (the first one fixed, its pose as priors), landmarks with their
+    initial positions as optimised values, the first n_gcp of them with the true position as an uncertain prior."""
+    import numpy as np
+    cams = [camera(1 + m, list(sc["intrinsics"][m]), sigma=intr_sigma) for m in range(sc["intrinsics"].shape[0])]
+    lms = []
+    for l in range(sc["n_pts"]):
+        gcp = l < n_gcp
+        lms.append(landmark(100000 + l, prior=sc["pts_true"][l] if gcp else None, sigma=[gcp_sigma] * 3 if gcp else None, opt=sc["pts"][l]))
+    order = np.argsort(sc["obs_cam"], kind="stable")
+    first = np.searchsorted(sc["obs_cam"][order], np.arange(sc["n_cams"] + 1))
+    imgs = []
+    for c in range(sc["n_cams"]):
+        sel = order[first[c]:first[c + 1]]
+        obs = [image_landmark(10_000_000 + int(o), 100000 + int(sc["obs_pt"][o]), sc["obs_uv"][o], obs_sigma) for o in sel]
+        kw = {}
+        if c == 0:
+            kw = dict(t_prior=sc["t"][0], r_prior=sc["raxis"][0], fixed=True)
+        elif pose_sigma is not None:
+            kw = dict(t_prior=sc["t_true"][c], t_sigma=[pose_sigma[1]] * 3, r_prior=sc["raxis_true"][c], r_sigma=[pose_sigma[0]] * 3)
+        imgs.append(image(1000 + c, 1 + int(sc["cam_model"][c]), obs, opt_t=sc["t"][c], opt_r=sc["raxis"][c], **kw))
+    return write(path, lms, imgs, cams), order
