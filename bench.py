@@ -190,7 +190,7 @@ def bench_config(a, explicit=True):
                         + ("intrinsic blocks f, pp, k, t FREE (one shared model: two pseudo-cameras in the reduced system), " if getattr(a, "free_intrinsics", False) else "intrinsics constant, ")
                         + "first camera fixed, 4 GCP priors",
             "pcg_rel_tol": a.pcg_tol, "pcg_max_iters": a.pcg_max_iters, "jacobi_scaling": 1,
-            "linear_solver": ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; when a rank holds >= 64 MB of them the PCG streams them as block-sparse panels: only the 6x6 blocks of camera pairs that share a point); "
+            "linear_solver": ("Schur complement + dense FP64 Cholesky of the explicit S on the device (sba_options.linear_solver = 1, the reference's SPARSE_SCHUR-style direct solve; hand-written blocked factorisation, csrc/sba_kernels_dense.cu)") if getattr(a, "linear_solver", 0) == 1 else ("Schur complement + SCHUR_JACOBI PCG; S explicit (dense symmetric 384x384 tiles, rebuilt every LM iteration; when a rank holds >= 64 MB of them the PCG streams them as block-sparse panels: only the 6x6 blocks of camera pairs that share a point); "
                               "whole PCG solve = one persistent cooperative kernel (TMA bulk-copy ring); multi-GPU: partial tiles reduce-scattered, "
                               "every rank applies its slice, the 6*Nc partial is all-reduced inside that kernel over NVLink peer mailboxes") if explicit else
                              ("Schur complement + SCHUR_JACOBI PCG; implicit operator (two passes over the observations per CG iteration: the explicit "
