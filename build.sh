@@ -8,7 +8,7 @@ FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -ccbin $
 OUT=../libsba_b200.so
 mkdir -p ../build
 pids=()
-for f in sba_kernels sba_kernels_schur sba_kernels_op sba_kernels_mv sba_kernels_pcg sba_kernels_pcgsolve sba_kernels_misc sba_kernels_points sba_kernels_explicit sba_kernels_shared sba_kernels_pairs sba_kernels_dense sba_solver; do
+for f in sba_kernels sba_kernels_schur sba_kernels_op sba_kernels_mv sba_kernels_pcg sba_kernels_pcgsolve sba_kernels_misc sba_kernels_points sba_kernels_explicit sba_kernels_shared sba_kernels_pairs sba_kernels_dense sba_noalloc sba_solver; do
   $NVCC $FLAGS -c $f.cu -o ../build/$f.o &
   pids+=($!)
 done

@@ -406,6 +406,31 @@ int sba_project_write_results(sba_project* p, const double* raxis, const double*
 /* Project::save: the document as indented JSON with sorted keys (what QJsonDocument::toJson writes) */
 int sba_project_save(const sba_project* p, const char* path);
 
+/* ---- Triangulation without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The same kernels as sba_triangulate (pose cache + batched multi-view DLT), stateless: no handle, every
+ * argument except the sizes is a DEVICE pointer, the work is enqueued on `stream` (a cudaStream_t; NULL = the default stream)
+ * and the call returns without synchronising.  It calls no cudaMalloc / cudaFree / allocating library routine: the camera
+ * cache and the sanitised index arrays live in ONE file-scope `static __device__` array of SBA_NOALLOC_SCRATCH_BYTES that
+ * every GPU loading the library holds until exit (csrc/sba_noalloc.cu).  Limits: n_cams <= SBA_NOALLOC_MAX_CAMS, n_points <=
+ * SBA_NOALLOC_MAX_POINTS, n_views <= SBA_NOALLOC_MAX_VIEWS; beyond them SBA_ERR_INVALID with the limits in sba_create_error()
+ * (the error text of handle-less calls) -- split the batch, or use sba_triangulate.
+ *   raxis, t [3 n_cams] sensor -> world poses; cam_model [n_cams] or NULL (all cameras use model 0); intr10 [10 n_models];
+ *   view_off [n_points + 1] (views of point i are view_off[i] .. view_off[i+1], n_views = view_off[n_points]), view_cam [n_views],
+ *   view_uv [2 n_views]; xyz_out [3 n_points]; ok_out [n_points] or NULL.
+ * A point with an offset, camera or camera-model index out of range gets xyz = 0, ok = 0 (nothing is read out of bounds).
+ * The scratch is shared by all calls on a device and keeps the last call's contents: every region a call reads is rewritten by
+ * that call first (nothing has to start at zero), calls on ONE stream are safe back to back, calls that overlap on the GPU
+ * (different streams, no dependency) RACE.  The first call on a device looks the array's address up (cudaGetSymbolAddress):
+ * make it outside a capture -- n_points = 0 does only that. */
+#define SBA_NOALLOC_MAX_CAMS 4096
+#define SBA_NOALLOC_MAX_POINTS 262144
+#define SBA_NOALLOC_MAX_VIEWS 1048576
+#define SBA_NOALLOC_SCRATCH_BYTES (6656 * 1024)
+int sba_triangulate_noalloc(int32_t n_cams, const double* raxis, const double* t, const int32_t* cam_model, int32_t n_models,
+                            const double* intr10, int32_t n_points, int32_t n_views, const int32_t* view_off,
+                            const int32_t* view_cam, const double* view_uv, double* xyz_out, uint8_t* ok_out, void* stream);
+
 const char* sba_version(void);
 
 #ifdef __cplusplus

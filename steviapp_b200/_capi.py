@@ -31,6 +31,7 @@ EXPORTS = [
     "sba_point_covariances", "sba_add_uv_pairs", "sba_set_pair_loss", "sba_evaluate_pairs",
     "sba_project_open", "sba_project_close", "sba_project_error", "sba_project_sizes", "sba_project_ids", "sba_project_convert",
     "sba_project_write_results", "sba_project_save",
+    "sba_triangulate_noalloc",
 ]
 
 
@@ -147,6 +148,7 @@ def load():
     lib.sba_project_convert.argtypes = [vp, i32] + [vp] * 20 + [P(i32)]
     lib.sba_project_write_results.argtypes = [vp, vp, vp, vp, vp]
     lib.sba_project_save.argtypes = [vp, C.c_char_p]
+    lib.sba_triangulate_noalloc.argtypes = [i32, vp, vp, vp, i32, vp, i32, i32, vp, vp, vp, vp, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if fn.restype is C.c_int:   # default restype: all status-returning functions

@@ -100,6 +100,15 @@ int sba_triangulate(sba_solver* s, int32_t n_points, const int32_t* view_off, co
                     double* xyz_out, uint8_t* ok_out, double* ms_kernel) {
     GUARD(s); return s->impl.triangulate(n_points, view_off, view_cam, view_uv, xyz_out, ok_out, ms_kernel);
 }
+int sba_triangulate_noalloc(int32_t n_cams, const double* raxis, const double* t, const int32_t* cam_model, int32_t n_models,
+                            const double* intr10, int32_t n_points, int32_t n_views, const int32_t* view_off,
+                            const int32_t* view_cam, const double* view_uv, double* xyz_out, uint8_t* ok_out, void* stream) {
+    std::string err;
+    const int rc = sba::triangulate_noalloc(n_cams, raxis, t, cam_model, n_models, intr10, n_points, n_views, view_off, view_cam,
+                                            view_uv, xyz_out, ok_out, stream, err);
+    if (rc) g_create_error = err;
+    return rc;
+}
 int sba_evaluate_intrinsics_jacobian(sba_solver* s, double* jac_intr) { GUARD(s); return s->impl.evaluate_intrinsics_jacobian(jac_intr); }
 int sba_evaluate_offset(sba_solver* s, const double* off12, double* residuals, double* jac_cam, double* jac_pt, int32_t* n_failed) {
     GUARD(s); return s->impl.evaluate_offset(off12, residuals, jac_cam, jac_pt, n_failed);

@@ -174,4 +174,9 @@ private:
     void unpin_all();
 };
 
+// sba_noalloc.cu: stateless DLT on device pointers, all scratch in one static __device__ array (sba_triangulate_noalloc)
+int triangulate_noalloc(int32_t n_cams, const double* raxis, const double* t, const int32_t* cam_model, int32_t n_models,
+                        const double* intr10, int32_t n_points, int32_t n_views, const int32_t* view_off, const int32_t* view_cam,
+                        const double* view_uv, double* xyz_out, uint8_t* ok_out, void* stream, std::string& err);
+
 }  // namespace sba
