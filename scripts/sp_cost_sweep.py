@@ -11,8 +11,10 @@ shape = sys.argv[1] if len(sys.argv) > 1 else "venice"
 sc = synthetic.make_scene(shape)
 fixed = dict(function_tolerance=0.0, parameter_tolerance=0.0, gradient_tolerance=0.0)
 os.environ["SBA_PS_SPARSE"] = "1"
-for panel in (1024, 2048, 3072, 4608):
-    for seg in (131072, 262144, 393216):
+grid = [(int(a), int(b)) for a, b in (x.split(":") for x in sys.argv[2].split(","))] if len(sys.argv) > 2 else \
+    [(panel, seg) for panel in (1024, 2048, 3072, 4608) for seg in (131072, 262144, 393216)]
+for panel, seg in grid:
+    if True:
         os.environ["SBA_SP_PANEL_COST"] = str(panel)
         os.environ["SBA_SP_SEG_COST"] = str(seg)
         s = SBASolver(pcg_check_every=8, **fixed)

@@ -10,6 +10,8 @@
 //   K2..K4 : the Schur elimination / SCHUR_JACOBI PCG / back-substitution that ceres::Solve
 //            performs for the reference (modularsbasolver.cpp:938); in-tree analogue
 //            modules/g2o/g2o/core/block_solver.hpp:329-479, solvers/pcg/linear_solver_pcg.hpp:84-165
+#include <cstdlib>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -98,8 +100,48 @@ void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
 // materialised Jacobian; here J_t = -J_X is not stored and J_r = A [R Pbar]x Q^T is rebuilt by its
 // readers from A and Pbar (rebuild_C), so 72 B/obs of it never exist.
 // ---------------------------------------------------------------------------
-template <bool JAC>
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 4) k_residual_jacobian(DevProblem P) {
+// one observation of the tile: residual, A, Pbar (and the d_z scale) into the camera-order planes
+template <bool JAC, bool INFO>
+__device__ __forceinline__ void k1_slot(const DevProblem& P, const double* cc, const double* intr, int spherical, size_t Ns, int s,
+                                        double2 uv, const double (&X)[3], double& acc, int& bad) {
+    double d[3];
+    dir_from_uv(uv.x, uv.y, intr, d);
+    double W[4] = {1.0, 0.0, 0.0, 1.0};
+    if (INFO) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) W[i] = __ldcs(P.obs_info + i * Ns + s);
+    }
+    double r[2] = {0.0, 0.0}, Jc[12], Jp[6], aux[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    const bool ok = obs_eval<JAC>(cc, X, d, INFO ? W : nullptr, spherical, r, Jc, Jp, JAC ? aux : nullptr);
+    if (!ok) {
+        bad = 1;
+        aux[0] = aux[1] = aux[2] = 0.0;   // Pbar = 0 marks a failed row for the factored pass
+        r[0] = r[1] = 0.0;
+        if (JAC) {
+#pragma unroll
+            for (int i = 0; i < 12; i++) Jc[i] = 0.0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) Jp[i] = 0.0;
+        }
+    }
+    acc += r[0] * r[0] + r[1] * r[1];
+    if (JAC) {
+        stcs(P.res + (s), r[0]);
+        stcs(P.res + (Ns + s), r[1]);
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            stcs(P.Ac + ((size_t)j * Ns + s), Jp[j]);
+            stcs(P.Ac + ((size_t)(3 + j) * Ns + s), Jp[3 + j]);
+        }
+        stcs(P.Pc + (s), aux[0]); stcs(P.Pc + (Ns + s), aux[1]); stcs(P.Pc + (2 * Ns + s), aux[2]);
+        if (P.Kc) { stcs(P.Kc + (s), aux[3]); stcs(P.Kc + (Ns + s), aux[4]); }
+    }
+}
+// PIPE: the loads of the lane's next observation (index two steps ahead, pixel and point one step ahead) are in flight
+// during the arithmetic of the current one -- the kernel is bound by the latency of the index -> point-gather chain
+// (ncu r2f: FP64 pipe 20 %, DRAM 46 %, 42 % warps active), not by bytes or flops.
+template <bool JAC, bool PIPE, int MINB, bool INFO>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB) k_residual_jacobian(DevProblem P) {
     __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
@@ -113,47 +155,36 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 4) k_residual_jacobian(D
     const double* intr = cc + CAM_CACHE_STRIDE;
     const int spherical = P.cam_kind[cam];
     const size_t Ns = (size_t)P.Ns;
+    const int end = start + len;
     double acc = 0.0;
     int bad = 0;
-    for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldcs(P.obs_pt + s);
-        if (pt < 0) continue;   // padding slot: planes stay zero
-        const double2 uv = ldcs2(P.obs_uv + 2 * (size_t)s);
-        const double2 x01 = ldg2(P.pts + 4 * (size_t)pt), x23 = ldg2(P.pts + 4 * (size_t)pt + 2);
-        const double X[3] = {x01.x, x01.y, x23.x};
-        double d[3];
-        dir_from_uv(uv.x, uv.y, intr, d);
-        double W[4];
-        const double* Wp = nullptr;
-        if (P.obs_info) {
-#pragma unroll
-            for (int i = 0; i < 4; i++) W[i] = __ldcs(P.obs_info + i * Ns + s);
-            Wp = W;
+    if (!PIPE) {
+        for (int s = start + lane; s < end; s += 32) {
+            const int pt = __ldcs(P.obs_pt + s);
+            if (pt < 0) continue;   // padding slot: planes stay zero
+            const double2 uv = ldcs2(P.obs_uv + 2 * (size_t)s);
+            const d4 Xp = ld256(P.pts + 4 * (size_t)pt);   // one 32-byte sector, one request
+            const double X[3] = {Xp.x, Xp.y, Xp.z};
+            k1_slot<JAC, INFO>(P, cc, intr, spherical, Ns, s, uv, X, acc, bad);
         }
-        double r[2] = {0.0, 0.0}, Jc[12], Jp[6], aux[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-        const bool ok = obs_eval<JAC>(cc, X, d, Wp, spherical, r, Jc, Jp, JAC ? aux : nullptr);
-        if (!ok) {
-            bad = 1;
-            aux[0] = aux[1] = aux[2] = 0.0;   // Pbar = 0 marks a failed row for the factored pass
-            r[0] = r[1] = 0.0;
-            if (JAC) {
-#pragma unroll
-                for (int i = 0; i < 12; i++) Jc[i] = 0.0;
-#pragma unroll
-                for (int i = 0; i < 6; i++) Jp[i] = 0.0;
+    } else {
+        int s = start + lane;
+        int pt1 = s < end ? __ldcs(P.obs_pt + s) : -1;
+        int pt2 = s + 32 < end ? __ldcs(P.obs_pt + s + 32) : -1;
+        double2 uv1 = s < end ? ldcs2(P.obs_uv + 2 * (size_t)s) : make_double2(0.0, 0.0);
+        d4 X1 = ld256(P.pts + 4 * (size_t)max(pt1, 0));
+        for (; s < end; s += 32) {
+            const int pt = pt1;
+            const double2 uv = uv1;
+            const double X[3] = {X1.x, X1.y, X1.z};
+            pt1 = pt2;
+            pt2 = s + 64 < end ? __ldcs(P.obs_pt + s + 64) : -1;
+            if (s + 32 < end) {
+                uv1 = ldcs2(P.obs_uv + 2 * (size_t)(s + 32));
+                X1 = ld256(P.pts + 4 * (size_t)max(pt1, 0));
             }
-        }
-        acc += r[0] * r[0] + r[1] * r[1];
-        if (JAC) {
-            stcs(P.res + (s), r[0]);
-            stcs(P.res + (Ns + s), r[1]);
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-                stcs(P.Ac + ((size_t)j * Ns + s), Jp[j]);
-                stcs(P.Ac + ((size_t)(3 + j) * Ns + s), Jp[3 + j]);
-            }
-            stcs(P.Pc + (s), aux[0]); stcs(P.Pc + (Ns + s), aux[1]); stcs(P.Pc + (2 * Ns + s), aux[2]);
-            if (P.Kc) { stcs(P.Kc + (s), aux[3]); stcs(P.Kc + (Ns + s), aux[4]); }
+            if (pt < 0) continue;
+            k1_slot<JAC, INFO>(P, cc, intr, spherical, Ns, s, uv, X, acc, bad);
         }
     }
     acc = warp_sum(acc);
@@ -166,8 +197,26 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 4) k_residual_jacobian(D
 void launch_residual_jacobian(const DevProblem& P, bool jac, cudaStream_t st) {
     if (P.Nt == 0) return;
     const int nb = cdiv(P.Nt, WARPS_PER_BLOCK);
-    if (jac) k_residual_jacobian<true><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
-    else k_residual_jacobian<false><<<nb, WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    const char* e = std::getenv("SBA_K1_PIPE");   // measurement knobs
+    const bool pipe = e ? std::atoi(e) != 0 : true;
+    const char* e2 = std::getenv("SBA_K1_MINB");
+    // measured on the Venice shape (scripts/ab_k1.py): K1 0.1268 ms with the prefetch at 3 blocks / SM (80 registers, no spills)
+    // vs 0.1367 without it (64 registers, 4 blocks) and 0.162 with it at 64 registers (spills); K1c 0.049 vs 0.066
+    const int minb = e2 ? std::atoi(e2) : (pipe ? (jac ? 3 : 4) : 4);
+    const int nt = WARPS_PER_BLOCK * 32;
+#define K1_LAUNCH(J, PP, MB)                                                        \
+    do {                                                                            \
+        if (P.obs_info) k_residual_jacobian<J, PP, MB, true><<<nb, nt, 0, st>>>(P); \
+        else k_residual_jacobian<J, PP, MB, false><<<nb, nt, 0, st>>>(P);           \
+    } while (0)
+    if (jac) {
+        if (pipe) { if (minb == 4) K1_LAUNCH(true, true, 4); else if (minb == 2) K1_LAUNCH(true, true, 2); else K1_LAUNCH(true, true, 3); }
+        else { if (minb == 3) K1_LAUNCH(true, false, 3); else K1_LAUNCH(true, false, 4); }
+    } else {
+        if (pipe) { if (minb == 4) K1_LAUNCH(false, true, 4); else if (minb == 2) K1_LAUNCH(false, true, 2); else K1_LAUNCH(false, true, 3); }
+        else { if (minb == 3) K1_LAUNCH(false, false, 3); else K1_LAUNCH(false, false, 4); }
+    }
+#undef K1_LAUNCH
 }
 
 }  // namespace sba

@@ -5,6 +5,8 @@
 // (SchurEliminator / ImplicitSchurComplement / SchurJacobiPreconditioner); the
 // in-tree statement of the same algebra is g2o's BlockSolver::solve
 // (modules/g2o/g2o/core/block_solver.hpp:329-479).
+#include <cstdlib>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -108,36 +110,86 @@ void launch_prior_blocks(const DevProblem& P, int cameras, cudaStream_t st) {
 // sums the tiles of each camera in tile order.
 // Reads 88 B/obs (res, A, Pbar planes, coalesced); C rebuilt in registers.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_camera_blocks(DevProblem P) {
+// PIPE: Rt lives in shared memory (12 doubles per warp) and the 11 plane values of the lane's NEXT slot are loaded before the
+// arithmetic of the current one: a pure stream at 16 warps / SM (120 registers) did not keep enough bytes in flight (0.58 of HBM).
+struct K2bIn { double A[6], p[3], r[2]; };
+__device__ __forceinline__ void k2b_load(const DevProblem& P, size_t Ns, int s, K2bIn& x) {
+#pragma unroll
+    for (int a = 0; a < 6; a++) x.A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
+    x.p[0] = __ldcs(P.Pc + s); x.p[1] = __ldcs(P.Pc + Ns + s); x.p[2] = __ldcs(P.Pc + 2 * Ns + s);
+    x.r[0] = __ldcs(P.res + s); x.r[1] = __ldcs(P.res + Ns + s);
+}
+__device__ __forceinline__ void k2b_accumulate(const K2bIn& x, const double* Rt, double (&H)[21], double (&g)[6]) {
+    double j0[6], j1[6], w[6];   // the two pre-Q rows J' = [A x d | -A] (Jc = J' diag(Q, I)^T, applied per camera by k_preq_finish)
+    preq_rows(x.A, x.p[0], x.p[1], x.p[2], Rt, w);
+#pragma unroll
+    for (int a = 0; a < 3; a++) { j0[a] = w[a]; j1[a] = w[3 + a]; j0[3 + a] = -x.A[a]; j1[3 + a] = -x.A[3 + a]; }
+    int q = 0;
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+        g[a] += j0[a] * x.r[0] + j1[a] * x.r[1];
+#pragma unroll
+        for (int b = a; b < 6; b++) H[q++] += j0[a] * j0[b] + j1[a] * j1[b];
+    }
+}
+template <int PIPE>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, 2) k_camera_blocks(DevProblem P) {
+    __shared__ double s_rt[PIPE ? WARPS_PER_BLOCK : 1][12];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
     if (tile >= P.Nt) return;
-    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    const int start = __ldg(P.tile_start + tile), end = start + __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
-    double Rt[12];
-    load_rt(P, __ldg(P.tile_cam + tile), Rt);
     double H[21], g[6];
 #pragma unroll
     for (int i = 0; i < 21; i++) H[i] = 0.0;
 #pragma unroll
     for (int i = 0; i < 6; i++) g[i] = 0.0;
-    for (int s = start + lane; s < start + len; s += 32) {
-        double j0[6], j1[6];   // the two pre-Q rows J' = [A x d | -A] (Jc = J' diag(Q, I)^T, applied per camera by k_preq_finish)
-        {
-            double A[6], w[6];
-#pragma unroll
-            for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
-            preq_rows(A, __ldcs(P.Pc + s), __ldcs(P.Pc + Ns + s), __ldcs(P.Pc + 2 * Ns + s), Rt, w);
-#pragma unroll
-            for (int a = 0; a < 3; a++) { j0[a] = w[a]; j1[a] = w[3 + a]; j0[3 + a] = -A[a]; j1[3 + a] = -A[3 + a]; }
+    if (!PIPE) {
+        double Rt[12];
+        load_rt(P, __ldg(P.tile_cam + tile), Rt);
+        for (int s = start + lane; s < end; s += 32) {
+            K2bIn x;
+            k2b_load(P, Ns, s, x);
+            k2b_accumulate(x, Rt, H, g);
         }
-        const double r0 = __ldcs(P.res + s), r1 = __ldcs(P.res + Ns + s);
-        int q = 0;
+    } else if (PIPE == 2) {
+        // two consecutive slots per lane, 128-bit loads: twice the bytes in flight per load instruction (tiles start on even slots
+        // and are padded to a multiple of 32: the pair never leaves the tile's padded range)
+        double* Rt = s_rt[warp];
+        {
+            const int cam = __ldg(P.tile_cam + tile);
+            if (lane < 9) Rt[lane] = __ldg(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam + lane);
+            else if (lane < 12) Rt[lane] = __ldg(P.cam_Q + 12 * (size_t)cam + lane);
+        }
+        __syncwarp();
+        for (int s = start + 2 * lane; s < end; s += 64) {
+            K2bIn x0, x1;
 #pragma unroll
-        for (int a = 0; a < 6; a++) {
-            g[a] += j0[a] * r0 + j1[a] * r1;
+            for (int a = 0; a < 6; a++) { const double2 v = ldcs2(P.Ac + (size_t)a * Ns + s); x0.A[a] = v.x; x1.A[a] = v.y; }
 #pragma unroll
-            for (int b = a; b < 6; b++) H[q++] += j0[a] * j0[b] + j1[a] * j1[b];
+            for (int a = 0; a < 3; a++) { const double2 v = ldcs2(P.Pc + (size_t)a * Ns + s); x0.p[a] = v.x; x1.p[a] = v.y; }
+#pragma unroll
+            for (int a = 0; a < 2; a++) { const double2 v = ldcs2(P.res + (size_t)a * Ns + s); x0.r[a] = v.x; x1.r[a] = v.y; }
+            k2b_accumulate(x0, Rt, H, g);
+            k2b_accumulate(x1, Rt, H, g);
+        }
+    } else {
+        double* Rt = s_rt[warp];
+        {
+            const int cam = __ldg(P.tile_cam + tile);
+            if (lane < 9) Rt[lane] = __ldg(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam + lane);
+            else if (lane < 12) Rt[lane] = __ldg(P.cam_Q + 12 * (size_t)cam + lane);   // dt = ts - t behind Q (load_rt)
+        }
+        __syncwarp();
+        int s = start + lane;
+        K2bIn cur, nxt;
+        if (s < end) k2b_load(P, Ns, s, cur);
+        for (; s < end; s += 32) {
+            const bool more = s + 32 < end;
+            if (more) k2b_load(P, Ns, s + 32, nxt);
+            k2b_accumulate(cur, Rt, H, g);
+            if (more) cur = nxt;
         }
     }
     double* out = P.tile_part + (size_t)TP * tile;
@@ -186,7 +238,16 @@ void launch_preq_finish(const DevProblem& P, double* H21, double* g6, cudaStream
     k_preq_finish<<<cdiv(P.Nc, 128), 128, 0, st>>>(P, H21, g6);
 }
 void launch_camera_blocks(const DevProblem& P, cudaStream_t st) {
-    if (P.Nt) k_camera_blocks<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    const char* e = std::getenv("SBA_K2B_PIPE");   // measurement knob
+    // Venice shape, stage 9 (scripts/ab_tiles.py): 0.1104 ms with two slots per lane, 0.1134 plain, 0.1238 with the prefetch
+    // (126 registers and the register moves of the rotation cost more than the overlap gives); a chunk-blocked plane layout
+    // ([256 slots][plane]) read through the same kernel was no faster (0.1135): the plane stride is not what limits it
+    const int pipe = e ? std::atoi(e) : 2;
+    if (P.Nt) {
+        if (pipe == 2 && P.Ns % 2 == 0) k_camera_blocks<2><<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+        else if (pipe == 1) k_camera_blocks<1><<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+        else k_camera_blocks<0><<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P);
+    }
     k_tile_reduce<<<cdiv(P.Nc * 21, 256), 256, 0, st>>>(P, 0, 21, P.Hcc, 1);
     k_tile_reduce<<<cdiv(P.Nc * 6, 256), 256, 0, st>>>(P, 21, 6, P.gc, 1);
     launch_preq_finish(P, P.Hcc, P.gc, st);
