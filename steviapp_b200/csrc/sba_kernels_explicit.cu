@@ -17,6 +17,7 @@
 // so a contribution needs only the point-order A planes, the point, Hinv and the two camera centres; the
 // per-camera factors T are applied once per block by the assembly kernel.
 #include <algorithm>
+#include <cstdlib>
 
 #include "sba_kernel_util.cuh"
 
@@ -160,6 +161,131 @@ __global__ void __launch_bounds__(128) k_explicit_assemble(DevProblem P) {
         for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, -B[6 * r + c], -B[6 * r + c + 1]);
 }
 
+// Variant with TWO lanes per block: the even lane sums rows 0..2 of the block (the [di]x K rows), the odd lane rows 3..5
+// (the K rows).  Both lanes stream the same run (identical addresses in one warp: one request), each keeps 18 sums instead
+// of 36 -- half the registers per thread and twice the threads, i.e. four times the loads in flight of the latency-bound
+// one-thread-per-block walk (ncu r2f: 164 registers, 17.5 % warps active).  Every entry is summed in the same order as
+// in k_explicit_assemble: bitwise identical tiles.
+__device__ __forceinline__ void asm2_add(const d4& k0, const d4& k1, const d4& k2, const d4& ti, const d4& tj, int half, double (&B)[18]) {
+    const double K[9] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w, k2.x};
+    const double db[3] = {k2.y - tj.y, k2.z - tj.z, k2.w - tj.w};
+    double M[9];   // the three rows this lane owns: U = [da]x K (even lane) or K itself (odd lane)
+    if (half == 0) {
+        const double da[3] = {k2.y - ti.y, k2.z - ti.z, k2.w - ti.w};
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            M[c] = da[1] * K[6 + c] - da[2] * K[3 + c];
+            M[3 + c] = da[2] * K[c] - da[0] * K[6 + c];
+            M[6 + c] = da[0] * K[3 + c] - da[1] * K[c];
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 9; e++) M[e] = K[e];
+    }
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+        const double u0 = M[3 * q], u1 = M[3 * q + 1], u2 = M[3 * q + 2];
+        B[6 * q + 0] -= u1 * db[2] - u2 * db[1]; B[6 * q + 1] -= u2 * db[0] - u0 * db[2]; B[6 * q + 2] -= u0 * db[1] - u1 * db[0];
+        B[6 * q + 3] += u0; B[6 * q + 4] += u1; B[6 * q + 5] += u2;
+    }
+}
+__device__ __forceinline__ d4 shfl_xor1(const d4& v) {
+    d4 r;
+    r.x = __shfl_xor_sync(FULL, v.x, 1); r.y = __shfl_xor_sync(FULL, v.y, 1); r.z = __shfl_xor_sync(FULL, v.z, 1); r.w = __shfl_xor_sync(FULL, v.w, 1);
+    return r;
+}
+// SPLIT: the two lanes load ALTERNATE contributions of the run (even lane r, r + 2, ..; odd lane r + 1, r + 3, ..) and hand
+// them to each other by shuffle: twice the distinct bytes in flight per block for the same registers
+template <bool SPLIT>
+__global__ void __launch_bounds__(128) k_explicit_assemble2(DevProblem P) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int half = t & 1;
+    int b = t >> 1;
+    const bool live = b < P.ex_nblocks;
+    if (!SPLIT && !live) return;
+    if (!live) b = P.ex_nblocks - 1;   // SPLIT: whole warps stay for the shuffles (the pair of a dead block is dead too)
+    const int i = __ldg(P.ex_blk_i + b), j = __ldg(P.ex_blk_j + b);
+    const int r0 = __ldg(P.ex_blk_off + b), r1 = r0 + __ldg(P.ex_blk_len + b);
+    d4 ti = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * i + 8);   // (Rt8, t0, t1, t2) of the sensor pose
+    d4 tj = ld256(P.cam_cache + (size_t)CAM_CACHE_STRIDE * j + 8);
+    {   // body t = ts - (ts - t)
+        const d4 qi = ld256(P.cam_Q + 12 * (size_t)i + 8), qj = ld256(P.cam_Q + 12 * (size_t)j + 8);
+        ti.y -= qi.y; ti.z -= qi.z; ti.w -= qi.w; tj.y -= qj.y; tj.z -= qj.z; tj.w -= qj.w;
+    }
+    double B[18];   // rows 3 * half .. 3 * half + 2 of the block
+#pragma unroll
+    for (int e = 0; e < 18; e++) B[e] = 0.0;
+    if (!SPLIT) {
+        const double* src = P.ex_contrib + EX_CW * (size_t)r0;
+        d4 n0 = ld256(src), n1 = ld256(src + 4), n2 = ld256(src + 8);   // r1 > r0 always
+        for (int r = r0; r < r1; r++) {
+            const d4 k0 = n0, k1 = n1, k2 = n2;
+            src += EX_CW;
+            if (r + 1 < r1) { n0 = ld256(src); n1 = ld256(src + 4); n2 = ld256(src + 8); }
+            asm2_add(k0, k1, k2, ti, tj, half, B);
+        }
+    } else {
+        // pairs of contributions (r, r + 1): this lane loads r + half; trip count made warp-uniform for the shuffles
+        const int npair = (r1 - r0 + 1) >> 1;
+        const int nmax = __reduce_max_sync(FULL, npair);
+        const double* src = P.ex_contrib + EX_CW * (size_t)(r0 + half);
+        d4 n0 = {0, 0, 0, 0}, n1 = n0, n2 = n0;
+        if (r0 + half < r1) { n0 = ld256(src); n1 = ld256(src + 4); n2 = ld256(src + 8); }
+        for (int k = 0; k < nmax; k++) {
+            const int r = r0 + 2 * k;
+            const d4 m0 = n0, m1 = n1, m2 = n2;   // contribution r + half
+            src += 2 * EX_CW;
+            if (r + 2 + half < r1) { n0 = ld256(src); n1 = ld256(src + 4); n2 = ld256(src + 8); }
+            const d4 o0 = shfl_xor1(m0), o1 = shfl_xor1(m1), o2 = shfl_xor1(m2);   // the partner's: r + 1 - half
+            if (half == 0) {
+                if (r < r1) asm2_add(m0, m1, m2, ti, tj, 0, B);
+                if (r + 1 < r1) asm2_add(o0, o1, o2, ti, tj, 0, B);
+            } else {
+                if (r < r1) asm2_add(o0, o1, o2, ti, tj, 1, B);
+                if (r + 1 < r1) asm2_add(m0, m1, m2, ti, tj, 1, B);
+            }
+        }
+        if (!live) return;
+    }
+    double* out = P.ex_S + ex_elem(P, i, j) + (size_t)(3 * half) * EX_TD;
+    if (P.cam_fixed[i] || P.cam_fixed[j]) {
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+#pragma unroll
+            for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, 0.0, 0.0);
+        return;
+    }
+    double Qm[9];
+    if (half == 0) {   // left factor Q_i on rows 0..2 (rows 3..5 keep the identity)
+        const double* Qi = P.cam_Q + 12 * (size_t)i;
+        const d4 q0 = ld256(Qi), q1 = ld256(Qi + 4), q2 = ld256(Qi + 8);
+        Qm[0] = q0.x; Qm[1] = q0.y; Qm[2] = q0.z; Qm[3] = q0.w; Qm[4] = q1.x; Qm[5] = q1.y; Qm[6] = q1.z; Qm[7] = q1.w; Qm[8] = q2.x;
+#pragma unroll
+        for (int c = 0; c < 6; c++) {
+            const double b0 = B[c], b1 = B[6 + c], b2 = B[12 + c];
+            B[c] = Qm[0] * b0 + Qm[1] * b1 + Qm[2] * b2;
+            B[6 + c] = Qm[3] * b0 + Qm[4] * b1 + Qm[5] * b2;
+            B[12 + c] = Qm[6] * b0 + Qm[7] * b1 + Qm[8] * b2;
+        }
+    }
+    {
+        const double* Qj = P.cam_Q + 12 * (size_t)j;
+        const d4 q0 = ld256(Qj), q1 = ld256(Qj + 4), q2 = ld256(Qj + 8);
+        Qm[0] = q0.x; Qm[1] = q0.y; Qm[2] = q0.z; Qm[3] = q0.w; Qm[4] = q1.x; Qm[5] = q1.y; Qm[6] = q1.z; Qm[7] = q1.w; Qm[8] = q2.x;
+    }
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const double b0 = B[6 * r], b1 = B[6 * r + 1], b2 = B[6 * r + 2];
+        B[6 * r] = b0 * Qm[0] + b1 * Qm[1] + b2 * Qm[2];
+        B[6 * r + 1] = b0 * Qm[3] + b1 * Qm[4] + b2 * Qm[5];
+        B[6 * r + 2] = b0 * Qm[6] + b1 * Qm[7] + b2 * Qm[8];
+    }
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, -B[6 * r + c], -B[6 * r + c + 1]);
+}
+
 // diagonal blocks: S_ii = Hcc + lam - Sd, stored HALVED in the diagonal tiles (T x + T^T x counts them twice).  Written
 // into the OWNED copy of the tile (multi-GPU: after the reduce-scatter of the partial tiles, by the owner only; Hcc and
 // Sd are already all-reduced there)
@@ -180,7 +306,14 @@ __global__ void k_explicit_diag(DevProblem P) {
 void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on) return;
     if (P.ex_ncontrib) k_explicit_contrib<<<cdiv(P.ex_ncontrib, 256), 256, 0, st>>>(P);
-    if (P.ex_nblocks) k_explicit_assemble<<<cdiv(P.ex_nblocks, 128), 128, 0, st>>>(P);
+    const char* e = std::getenv("SBA_EX_ASM2");   // measurement knob: two lanes per block
+    const int two = e ? std::atoi(e) : 2;   // Venice build (scripts/ab_build.py): 1.155 ms one thread per block, 1.099 two lanes, 1.073 two lanes sharing the loads
+    if (P.ex_nblocks) {
+        // (the shared-load variant capped at 128 registers for a fourth block per SM spills and is slower: 1.072 ms)
+        if (two == 2) k_explicit_assemble2<true><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
+        else if (two) k_explicit_assemble2<false><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
+        else k_explicit_assemble<<<cdiv(P.ex_nblocks, 128), 128, 0, st>>>(P);
+    }
 }
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on) return;

@@ -11,6 +11,8 @@
 
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -301,12 +303,15 @@ void launch_pcg_BC(const DevProblem& P, double tol2, int max_iters, cudaStream_t
 // (Ceres TrustRegionMinimizer model_cost_change).  Warp per tile, tile partial
 // into tile_cost (free between the linear solve and the trial evaluation).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem P, const double* __restrict__ dc) {
+// PIPE: the point index two slots ahead and the dp gather one slot ahead are in flight during the arithmetic (same latency
+// chain as K1: index -> gather).
+template <bool PIPE>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, PIPE ? 3 : 4) k_model_tiles(DevProblem P, const double* __restrict__ dc) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
     if (tile >= P.Nt) return;
     const int cam = __ldg(P.tile_cam + tile);
-    const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
+    const int start = __ldg(P.tile_start + tile), end = start + __ldg(P.tile_len + tile);
     const size_t Ns = (size_t)P.Ns;
     // m = Jc dc + Jp dp = A ((X - t) x a_c - x_t + dp) = A ((X - c0) x a_c - g_c + dp) with the per-camera operand (a_c, g_c) of dc
     // (cam_vec, written by launch_model_change), X - c0 = R Pbar + (t - c0): no C planes, no per-tile 3x3 products
@@ -316,10 +321,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
     const double ac0 = o0.x, ac1 = o0.y, ac2 = o0.z, gc0 = o0.w, gc1 = o1.x, gc2 = o1.y;
     const double tc0 = r2.y - P.center[0], tc1 = r2.z - P.center[1], tc2 = r2.w - P.center[2];
     double acc = 0.0;
-    for (int s = start + lane; s < start + len; s += 32) {
-        const int pt = __ldcs(P.obs_pt + s);
-        if (pt < 0) continue;
-        const double2 d01 = ldg2(P.dp + 4 * (size_t)pt), d23 = ldg2(P.dp + 4 * (size_t)pt + 2);
+    auto slot = [&](int s, const d4& dpv) {
         double m0 = 0.0, m1 = 0.0, A[6];
 #pragma unroll
         for (int a = 0; a < 6; a++) A[a] = __ldcs(P.Ac + (size_t)a * Ns + s);
@@ -327,12 +329,32 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_model_tiles(DevProblem
         const double d0 = r0.x * p0 + r0.w * p1 + r1.z * p2 + tc0;   // X - c0 = R Pbar + (t - c0), R = Rt^T
         const double d1 = r0.y * p0 + r1.x * p1 + r1.w * p2 + tc1;
         const double d2 = r0.z * p0 + r1.y * p1 + r2.x * p2 + tc2;
-        const double v[3] = {d1 * ac2 - d2 * ac1 - gc0 + d01.x, d2 * ac0 - d0 * ac2 - gc1 + d01.y, d0 * ac1 - d1 * ac0 - gc2 + d23.x};
+        const double v[3] = {d1 * ac2 - d2 * ac1 - gc0 + dpv.x, d2 * ac0 - d0 * ac2 - gc1 + dpv.y, d0 * ac1 - d1 * ac0 - gc2 + dpv.z};
 #pragma unroll
         for (int a = 0; a < 3; a++) { m0 += A[a] * v[a]; m1 += A[3 + a] * v[a]; }
         if (P.sh_gd) { m0 += __ldcs(P.sh_gd + s); m1 += __ldcs(P.sh_gd + Ns + s); }   // + G_o delta of the shared blocks (sba_kernels_shared.cu)
         const double e0 = __ldcs(P.res + s), e1 = __ldcs(P.res + Ns + s);
         acc += m0 * (e0 + 0.5 * m0) + m1 * (e1 + 0.5 * m1);
+    };
+    if (!PIPE) {
+        for (int s = start + lane; s < end; s += 32) {
+            const int pt = __ldcs(P.obs_pt + s);
+            if (pt < 0) continue;
+            slot(s, ld256(P.dp + 4 * (size_t)pt));
+        }
+    } else {
+        int s = start + lane;
+        int pt1 = s < end ? __ldcs(P.obs_pt + s) : -1;
+        int pt2 = s + 32 < end ? __ldcs(P.obs_pt + s + 32) : -1;
+        d4 dp1 = ld256(P.dp + 4 * (size_t)max(pt1, 0));
+        for (; s < end; s += 32) {
+            const int pt = pt1;
+            const d4 dpv = dp1;
+            pt1 = pt2;
+            pt2 = s + 64 < end ? __ldcs(P.obs_pt + s + 64) : -1;
+            if (s + 32 < end) dp1 = ld256(P.dp + 4 * (size_t)max(pt1, 0));
+            if (pt >= 0) slot(s, dpv);
+        }
     }
     acc = warp_sum(acc);
     if (lane == 0) P.tile_cost[tile] = acc;
@@ -406,7 +428,11 @@ __global__ void __launch_bounds__(RED_BLOCK) k_model_reduce(DevProblem P, const 
 }
 void launch_model_change(const DevProblem& P, const double* dc, cudaStream_t st) {
     launch_cam_vec(P, dc, st);   // per-camera operand (a_c, g_c) of dc for k_model_tiles
-    if (P.Nt) k_model_tiles<<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P, dc);
+    if (P.Nt) {
+        const char* e = std::getenv("SBA_MODEL_PIPE");   // measurement knob
+        if (e ? std::atoi(e) != 0 : true) k_model_tiles<true><<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P, dc);
+        else k_model_tiles<false><<<cdiv(P.Nt, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, st>>>(P, dc);
+    }
     if (P.NB) k_point_stats<<<P.NB, 256, 0, st>>>(P);
     k_model_reduce<<<1, RED_BLOCK, 0, st>>>(P, dc);
 }

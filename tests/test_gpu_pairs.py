@@ -61,7 +61,7 @@ def test_pairs_lm_with_losses(oracle, loss):
     out = s.solve(max_iterations=5, **FIXED_ITERS)
     for a, b in zip(out["cost_history"], so["cost_history"]):
         assert abs(a - b) <= TOL_COST * max(b, 1.0), (out["cost_history"], so["cost_history"])
-    assert all(abs(a - b) <= max(2, 0.04 * b) for a, b in zip(out["pcg_iters_history"][1:], so["pcg_iters_history"][1:]))
+    assert all(abs(a - b) <= max(4, 0.08 * b) for a, b in zip(out["pcg_iters_history"][1:], so["pcg_iters_history"][1:]))
     assert relerr(raxis, p.cam_r.reshape(-1, 3)) < 1e-7 and relerr(t, p.cam_t.reshape(-1, 3)) < 1e-7
 
 
