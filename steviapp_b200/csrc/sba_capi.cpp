@@ -176,6 +176,7 @@ int sba_explicit_tiles(sba_solver* s, double* tiles, int32_t* tile_i, int32_t* t
     GUARD(s);
     const sba::DevProblem& P = s->impl.P;
     if (!P.ex_on || P.ex_Sown != P.ex_S) return SBA_ERR_INVALID;   // single-GPU inspection hook (a rank holds only its slice)
+    s->impl.ensure_dense_tiles();   // direct mode: the build keeps only the panels current
     cudaDeviceSynchronize();
     const size_t n = (size_t)P.ex_ntiles;
     if (tiles && cudaMemcpy(tiles, P.ex_S, n * 384 * 384 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return SBA_ERR_CUDA;

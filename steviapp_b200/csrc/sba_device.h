@@ -97,6 +97,13 @@ struct DevProblem {
     int32_t* ex_blk_j;    // ex_nblocks
     int32_t* ex_blk_off;  // ex_nblocks: first contribution of the block in the block-sorted buffer
     int32_t* ex_blk_len;  // ex_nblocks: run length; the block list is ordered by run length, longest first
+    // direct mode (single GPU, block-sparse panels, no shared blocks / factors): the assembly and the diagonal kernel write the
+    // panels of the persistent PCG kernel themselves; the dense tiles are brought up to date on demand (decompaction)
+    int32_t ex_direct;
+    int64_t* ex_blk_dst;  // ex_nblocks: offset (doubles) in sp_data of element (0, 0) of the block inside its panel
+    int32_t* ex_blk_m6;   // ex_nblocks: row stride of that panel
+    int64_t* ex_dg_dst;   // Nc(e): same for the diagonal block of every camera
+    int32_t* ex_dg_m6;
     double* ex_contrib;   // 12 * ex_ncontrib: compact contributions (K 3x3, X), block-sorted; expanded to D_i K D_j^T by the assembly
     double* ex_row;       // ex_nown * 384: row partials of the tile mat-vec (y_I += T x_J), local tile order
     double* ex_col;       // ex_nown * 6 * 384: column partials per 64-row chunk (y_J += T^T x_I); = ex_row + ex_nown * 384
@@ -314,6 +321,7 @@ void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t 
 // explicit reduced camera system
 void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> off-diagonal blocks of ex_S (needs Hinv of this LM iteration)
 void launch_explicit_sparse_dirs(const DevProblem& P, cudaStream_t st);   // chunk directories -> panel stream (once, at finalize)
+void launch_explicit_decompact(const DevProblem& P, cudaStream_t st);   // panels -> dense tiles (direct mode: for the hooks and the dense factorisation)
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st);   // dense tiles -> block-sparse panels (sp_on)
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st);      // diagonal blocks of the owned tiles (needs Hcc, Sd, lam_c; multi-GPU: after the reduce-scatter)
 void launch_explicit_matvec(const DevProblem& P, const double* x, cudaStream_t st, int pcg = 0, double tol2 = 0.0,

@@ -196,7 +196,7 @@ __device__ __forceinline__ d4 shfl_xor1(const d4& v) {
 }
 // SPLIT: the two lanes load ALTERNATE contributions of the run (even lane r, r + 2, ..; odd lane r + 1, r + 3, ..) and hand
 // them to each other by shuffle: twice the distinct bytes in flight per block for the same registers
-template <bool SPLIT>
+template <bool SPLIT, bool DIRECT>
 __global__ void __launch_bounds__(128) k_explicit_assemble2(DevProblem P) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int half = t & 1;
@@ -247,12 +247,14 @@ __global__ void __launch_bounds__(128) k_explicit_assemble2(DevProblem P) {
         }
         if (!live) return;
     }
-    double* out = P.ex_S + ex_elem(P, i, j) + (size_t)(3 * half) * EX_TD;
+    // DIRECT: straight into the block's place in its panel (row stride m6) -- no dense tile, no compaction pass
+    const size_t ld = DIRECT ? (size_t)__ldg(P.ex_blk_m6 + b) : (size_t)EX_TD;
+    double* out = DIRECT ? P.sp_data + __ldg(P.ex_blk_dst + b) + (size_t)(3 * half) * ld : P.ex_S + ex_elem(P, i, j) + (size_t)(3 * half) * EX_TD;
     if (P.cam_fixed[i] || P.cam_fixed[j]) {
 #pragma unroll
         for (int r = 0; r < 3; r++)
 #pragma unroll
-            for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, 0.0, 0.0);
+            for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * ld + c, 0.0, 0.0);
         return;
     }
     double Qm[9];
@@ -283,7 +285,7 @@ __global__ void __launch_bounds__(128) k_explicit_assemble2(DevProblem P) {
 #pragma unroll
     for (int r = 0; r < 3; r++)
 #pragma unroll
-        for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * EX_TD + c, -B[6 * r + c], -B[6 * r + c + 1]);
+        for (int c = 0; c < 6; c += 2) st2(out + (size_t)r * ld + c, -B[6 * r + c], -B[6 * r + c + 1]);
 }
 
 // diagonal blocks: S_ii = Hcc + lam - Sd, stored HALVED in the diagonal tiles (T x + T^T x counts them twice).  Written
@@ -303,6 +305,17 @@ __global__ void k_explicit_diag(DevProblem P) {
     P.ex_Sown[(size_t)tile * EX_TD * EX_TD + (size_t)(l + r) * EX_TD + l + cc] = 0.5 * v;
 }
 
+// direct mode: the (halved) diagonal block of every camera into its panel
+__global__ void k_explicit_diag_direct(DevProblem P) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= P.Nc * 36) return;
+    const int c = t / 36, e = t - 36 * c, r = e / 6, cc = e - 6 * r;
+    const int q = sym6(r, cc);
+    double v = P.Hcc[21 * (size_t)c + q] - P.Sd[21 * (size_t)c + q];
+    if (r == cc) v += P.lam_c[6 * (size_t)c + r];
+    P.sp_data[P.ex_dg_dst[c] + (size_t)r * P.ex_dg_m6[c] + cc] = 0.5 * v;
+}
+
 void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on) return;
     if (P.ex_ncontrib) k_explicit_contrib<<<cdiv(P.ex_ncontrib, 256), 256, 0, st>>>(P);
@@ -310,13 +323,15 @@ void launch_explicit_build(const DevProblem& P, cudaStream_t st) {
     const int two = e ? std::atoi(e) : 2;   // Venice build (scripts/ab_build.py): 1.155 ms one thread per block, 1.099 two lanes, 1.073 two lanes sharing the loads
     if (P.ex_nblocks) {
         // (the shared-load variant capped at 128 registers for a fourth block per SM spills and is slower: 1.072 ms)
-        if (two == 2) k_explicit_assemble2<true><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
-        else if (two) k_explicit_assemble2<false><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
+        if (P.ex_direct) k_explicit_assemble2<true, true><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
+        else if (two == 2) k_explicit_assemble2<true, false><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
+        else if (two) k_explicit_assemble2<false, false><<<cdiv(2 * P.ex_nblocks, 128), 128, 0, st>>>(P);
         else k_explicit_assemble<<<cdiv(P.ex_nblocks, 128), 128, 0, st>>>(P);
     }
 }
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st) {
     if (!P.ex_on) return;
+    if (P.ex_direct) { k_explicit_diag_direct<<<cdiv(P.Nc * 36, 256), 256, 0, st>>>(P); return; }
     k_explicit_diag<<<cdiv(P.Nc * 36, 256), 256, 0, st>>>(P);
 }
 
@@ -343,6 +358,25 @@ __global__ void __launch_bounds__(256) k_explicit_compact(DevProblem P) {
     uint4* map_out = reinterpret_cast<uint4*>(dst + 6 * m6);
     for (int k = lane; k < (2 * m6 + 15) / 16; k += 32) map_out[k] = __ldg(st4 + 1 + k);
 }
+// the inverse copy (direct mode keeps only the panels up to date): panel values back into their dense tile
+__global__ void __launch_bounds__(256) k_explicit_decompact(DevProblem P) {
+    const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= P.sp_npanel) return;
+    const int4 pn = __ldg(P.sp_panel + q);
+    const int m6 = pn.z;
+    const uint16_t* cmap = P.sp_idx + 8 * (size_t)pn.y + 8;
+    double* tile = P.ex_Sown + (size_t)(pn.w >> 6) * EX_TD * EX_TD + (size_t)(6 * (pn.w & 63)) * EX_TD;
+    const double* src = P.sp_data + 2 * (size_t)pn.x + 2;
+    for (int c = lane; c < m6; c += 32) {
+        const int cj = __ldg(cmap + c);
+#pragma unroll
+        for (int r = 0; r < 6; r++) tile[(size_t)r * EX_TD + cj] = src[r * m6 + c];
+    }
+}
+void launch_explicit_decompact(const DevProblem& P, cudaStream_t st) {
+    if (!P.ex_on || !P.sp_on || !P.sp_npanel) return;
+    k_explicit_decompact<<<cdiv(P.sp_npanel * 32, 256), 256, 0, st>>>(P);
+}
 __global__ void __launch_bounds__(256) k_explicit_sparse_dirs(DevProblem P) {
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (c >= P.sp_nchunk) return;
@@ -356,7 +390,7 @@ void launch_explicit_sparse_dirs(const DevProblem& P, cudaStream_t st) {
     k_explicit_sparse_dirs<<<cdiv(P.sp_nchunk * 32, 256), 256, 0, st>>>(P);
 }
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st) {
-    if (!P.ex_on || !P.ps_on || !P.sp_on) return;
+    if (!P.ex_on || !P.ps_on || !P.sp_on || P.ex_direct) return;   // direct mode: the panels are written by the assembly itself
     k_explicit_compact<<<cdiv(P.sp_npanel * 32, 256), 256, 0, st>>>(P);
 }
 

@@ -97,6 +97,7 @@ public:
     int schur_matvec(const double* lam_c, const double* lam_p, const double* x, double* y, double* rhs);
     int solve(int copy_params, sba_summary* sum);
     int time_stage(int stage, int reps, double* ms);
+    int ensure_dense_tiles();      // sba_solver_lm.inc: panels -> dense tiles when stale (hooks, dense factorisation, tile mat-vec)
     int triangulate(int32_t n_points, const int32_t* view_off, const int32_t* view_cam, const double* view_uv,
                     double* xyz_out, uint8_t* ok_out, double* ms_kernel);
     int comm_init(int rank, int nranks, const uint8_t* id128);
@@ -172,6 +173,7 @@ private:
     std::vector<Pinned> pinned;    // caller parameter arrays registered with cudaHostRegister (sba_solver_layout.inc)
     bool pin_caller(const void* p, size_t bytes);
     void unpin_all();
+    bool tiles_stale = false;      // direct mode: the panels were rebuilt since the dense tiles were last refreshed
 };
 
 // sba_noalloc.cu: stateless DLT on device pointers, all scratch in one static __device__ array (sba_triangulate_noalloc)
