@@ -1,7 +1,7 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, bench line, ncu launch lists (profiling target and bench.py) + full captures of the main kernels.
 # Usage (from the repo root on the GPU box): bash scripts/round_gpu.sh <tag>
-tag=${1:-r2f}
+tag=${1:-r2h}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -q > gpurun_out/${tag}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${tag}_pytest_gpu.log
 timeout 400 python bench.py --steps 20 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"

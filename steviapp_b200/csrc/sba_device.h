@@ -90,9 +90,7 @@ struct DevProblem {
     // in ex_Sown (local tile t = global tile - ex_own0) and applies only those.  Single GPU: ex_Sown = ex_S, all tiles.
     int32_t ex_own0, ex_nown;
     double* ex_Sown;
-    int32_t* ex_qa;       // ex_ncontrib: q slot of the first observation (smaller camera index), producer (point) order
-    int32_t* ex_qb;       // ex_ncontrib: q slot of the second observation
-    int32_t* ex_dest;     // ex_ncontrib: position of the contribution in block-sorted order
+    int4* ex_rec;         // ex_ncontrib: {qa, qb, dest, point} in one 16-byte record (what the producer kernel reads)
     int32_t* ex_blk_i;    // ex_nblocks
     int32_t* ex_blk_j;    // ex_nblocks
     int32_t* ex_blk_off;  // ex_nblocks: first contribution of the block in the block-sorted buffer

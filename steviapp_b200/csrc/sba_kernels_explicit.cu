@@ -33,9 +33,10 @@ constexpr int EX_CW = 12;   // doubles per stored contribution
 __global__ void __launch_bounds__(256) k_explicit_contrib(DevProblem P) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= P.ex_ncontrib) return;
-    const int qa = __ldcs(P.ex_qa + c), qb = __ldcs(P.ex_qb + c);
-    const size_t dest = (size_t)__ldcs(P.ex_dest + c);
-    const int pt = __ldg(P.q_pt + qa);
+    const int4 rec = __ldcs(P.ex_rec + c);   // {qa, qb, dest, point}
+    const int qa = rec.x, qb = rec.y;
+    const size_t dest = (size_t)rec.z;
+    const int pt = rec.w;
     const size_t Nq = (size_t)P.Nq;
     double Aa[6], Ab[6];
 #pragma unroll
