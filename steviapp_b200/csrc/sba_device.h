@@ -119,6 +119,10 @@ struct DevProblem {
                           //   uint4 ll[2][xchg_n][ps_nitems][128] = {lo, seq, hi, seq} per value (flag travels with the data)
     int32_t xchg_nflag;   // flags per (parity, source) = pcg_blocks
     double* xchg_peer[8]; // mailbox base of every rank (own entry = local pointer)
+    // multi-GPU build without ncclReduceScatter: the partial tiles of every rank are mapped into every process (CUDA IPC) and
+    // the owner of a slice PULLS it from all ranks over NVLink, summing in rank order (k_explicit_pull_reduce)
+    int32_t ex_pull;
+    double* ex_peer_S[8]; // ex_S of every rank (own entry = local pointer)
     uint32_t* xchg_ctr;   // local: number of exchanges completed so far (identical on every rank)
     // ---- persistent PCG kernel (sba_kernels_pcgsolve.cu): static schedule of the tile mat-vec and of the fold ----
     int32_t ps_on;        // 1: run_pcg launches k_pcg_solve once per LM iteration
@@ -319,6 +323,7 @@ void launch_unpack_points(const double* pts4, double* xyz3, int n, cudaStream_t 
 // explicit reduced camera system
 void launch_explicit_build(const DevProblem& P, cudaStream_t st);     // contributions -> off-diagonal blocks of ex_S (needs Hinv of this LM iteration)
 void launch_explicit_sparse_dirs(const DevProblem& P, cudaStream_t st);   // chunk directories -> panel stream (once, at finalize)
+void launch_explicit_pull_reduce(const DevProblem& P, int nranks, int rank, size_t slice_doubles, cudaStream_t st);   // ex_Sown = sum over the ranks of their slice of ex_S
 void launch_explicit_decompact(const DevProblem& P, cudaStream_t st);   // panels -> dense tiles (direct mode: for the hooks and the dense factorisation)
 void launch_explicit_compact(const DevProblem& P, cudaStream_t st);   // dense tiles -> block-sparse panels (sp_on)
 void launch_explicit_diag(const DevProblem& P, cudaStream_t st);      // diagonal blocks of the owned tiles (needs Hcc, Sd, lam_c; multi-GPU: after the reduce-scatter)

@@ -359,6 +359,48 @@ __global__ void __launch_bounds__(256) k_explicit_compact(DevProblem P) {
     uint4* map_out = reinterpret_cast<uint4*>(dst + 6 * m6);
     for (int k = lane; k < (2 * m6 + 15) / 16; k += 32) map_out[k] = __ldg(st4 + 1 + k);
 }
+// multi-GPU: this rank's slice of the summed tiles, pulled from the partial tiles of all ranks (peer memory over NVLink /
+// NVSwitch, own partial from HBM), summed in RANK ORDER -- same operands, same order on every run: deterministic.  Replaces
+// ncclReduceScatter on the 479 MB partial tiles; G loads of 32 bytes per thread in flight, two rounds unrolled.
+template <int G>
+__global__ void __launch_bounds__(256) k_explicit_pull_reduce(DevProblem P, size_t first, size_t n4) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
+        const size_t j = i + stride;
+        d4 a[G], b[G];
+#pragma unroll
+        for (int g = 0; g < G; g++) a[g] = ld256(P.ex_peer_S[g] + first + 4 * i);
+        if (j < n4) {
+#pragma unroll
+            for (int g = 0; g < G; g++) b[g] = ld256(P.ex_peer_S[g] + first + 4 * j);
+        }
+        d4 s = a[0];
+#pragma unroll
+        for (int g = 1; g < G; g++) { s.x += a[g].x; s.y += a[g].y; s.z += a[g].z; s.w += a[g].w; }
+        st256(P.ex_Sown + 4 * i, s.x, s.y, s.z, s.w);
+        if (j < n4) {
+            d4 u = b[0];
+#pragma unroll
+            for (int g = 1; g < G; g++) { u.x += b[g].x; u.y += b[g].y; u.z += b[g].z; u.w += b[g].w; }
+            st256(P.ex_Sown + 4 * j, u.x, u.y, u.z, u.w);
+        }
+    }
+}
+void launch_explicit_pull_reduce(const DevProblem& P, int nranks, int rank, size_t slice_doubles, cudaStream_t st) {
+    const size_t n4 = slice_doubles / 4, first = (size_t)rank * slice_doubles;
+    const int grid = 148 * 8;
+    switch (nranks) {
+        case 2: k_explicit_pull_reduce<2><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 3: k_explicit_pull_reduce<3><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 4: k_explicit_pull_reduce<4><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 5: k_explicit_pull_reduce<5><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 6: k_explicit_pull_reduce<6><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 7: k_explicit_pull_reduce<7><<<grid, 256, 0, st>>>(P, first, n4); break;
+        case 8: k_explicit_pull_reduce<8><<<grid, 256, 0, st>>>(P, first, n4); break;
+        default: break;
+    }
+}
+
 // the inverse copy (direct mode keeps only the panels up to date): panel values back into their dense tile
 __global__ void __launch_bounds__(256) k_explicit_decompact(DevProblem P) {
     const int q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;

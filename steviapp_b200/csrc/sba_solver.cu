@@ -26,6 +26,7 @@ Solver::Solver(const sba_options& o) : opt(o) {}
 Solver::~Solver() {
     if (st) cudaStreamSynchronize(st);
     release_peer_exchange();
+    release_peer_tiles();
     unpin_all();
     comm.destroy();
     timer.destroy();

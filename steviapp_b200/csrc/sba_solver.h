@@ -120,6 +120,7 @@ private:
     int build_rhs_and_preconditioner(bool* ok);            // damped inverse, reduced rhs, Minv
     int schur_apply(const double* x, double* y);           // y = S x  (x zero at fixed cameras)
     int run_pcg(int* iters);
+    int setup_peer_tiles();                  // sba_solver_hooks.inc: IPC mapping of every rank's partial tiles (pull-reduce of the build)
     int setup_peer_exchange();               // sba_solver_hooks.inc: IPC mailboxes of the fused PCG all-reduce (multi-GPU)
     int build_explicit_structure(const std::vector<int32_t>& pt_cnt, const std::vector<int32_t>& pt_q0,
                                  const std::vector<int32_t>& q_cam);   // sba_solver_explicit.inc
@@ -169,6 +170,9 @@ private:
     void* xchg_mailbox = nullptr;  // this rank's mailbox of the peer-memory all-reduce (own cudaMalloc: exported through CUDA IPC)
     std::vector<void*> ipc_opened; // peer mailboxes opened with cudaIpcOpenMemHandle
     void release_peer_exchange();
+    void* ex_S_ipc = nullptr;             // multi-GPU: the partial tiles in an allocation of their own (exported through CUDA IPC)
+    std::vector<void*> ipc_tiles_opened;  // peer partial tiles opened with cudaIpcOpenMemHandle
+    void release_peer_tiles();
     struct Pinned { const void* p; size_t bytes; bool ok; };
     std::vector<Pinned> pinned;    // caller parameter arrays registered with cudaHostRegister (sba_solver_layout.inc)
     bool pin_caller(const void* p, size_t bytes);
