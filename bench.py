@@ -469,7 +469,7 @@ def run_b200(a):
                "alg_GBps_survey_bytes": survey_bytes / best / 1e6, "frac_of_hbm_peak_survey_bytes": survey_bytes / best / 1e6 / peak,
                "streamed_GBps": stream_bytes / best / 1e6, "e2e_wall_s_with_host_copies": wall_d, "ok_fraction": float(okf.mean()),
                "max_abs_err_vs_truth_first_copy": float(np.abs(x[:truth["n_pts"]] - truth["pts_true"]).max()),
-               "note": "camera records (96 B) are gathered from L1/L2, only pixels + camera indices stream from HBM: the SURVEY byte count (poses and rays per view) is an upper bound of the traffic"}
+               "note": "camera records (64 B: quaternion + Rt t) are gathered from L1/L2, only pixels + camera indices stream from HBM: the SURVEY byte count (poses and rays per view) is an upper bound of the traffic"}
         reset()
 
     cpu = None

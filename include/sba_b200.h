@@ -426,7 +426,7 @@ int sba_project_save(const sba_project* p, const char* path);
 #define SBA_NOALLOC_MAX_CAMS 4096
 #define SBA_NOALLOC_MAX_POINTS 262144
 #define SBA_NOALLOC_MAX_VIEWS 1048576
-#define SBA_NOALLOC_SCRATCH_BYTES (6656 * 1024)
+#define SBA_NOALLOC_SCRATCH_BYTES (6912 * 1024)
 int sba_triangulate_noalloc(int32_t n_cams, const double* raxis, const double* t, const int32_t* cam_model, int32_t n_models,
                             const double* intr10, int32_t n_points, int32_t n_views, const int32_t* view_off,
                             const int32_t* view_cam, const double* view_uv, double* xyz_out, uint8_t* ok_out, void* stream);

@@ -108,6 +108,7 @@ struct DevProblem {
     int32_t* ex_fold_ptr; // ex_NT + 1
     int32_t* ex_fold_off; // offsets (doubles, relative to ex_row) of the partial vectors of every camera tile, fixed order
     double* cam_Q;        // 12*Nc: Q = (R Jr)^T row-major (9) + pad, written by K0: C = A [X - t]x Q^T
+    double* dlt_rec;      // 8*Nc: quaternion of Rt + Rt t per camera, written by launch_triangulate for its kernel (sba_math.cuh dlt_record)
     // ---- peer-memory all-reduce of the PCG operator partial (multi-GPU; sba_kernels_pcg.cu, PM_XCHG) ----
     // every rank owns a mailbox, mapped into every process (CUDA IPC, stores travel over NVLink / NVSwitch):
     //   double   data[2][xchg_n][xchg_stride]     (parity of the exchange number, source rank, vector element)

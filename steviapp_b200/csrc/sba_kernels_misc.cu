@@ -2,6 +2,8 @@
 // evaluate hook, layout conversion and K5 batched DLT triangulation.
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "sba_kernel_util.cuh"
 
 namespace sba {
@@ -208,12 +210,27 @@ void launch_set_lambda(const DevProblem& P, const double* lam_c, const double* l
 
 // ---------------------------------------------------------------------------
 // K5 batched multi-view DLT: thread per point, inhomogeneous normal equations accumulated over its views in registers,
-// closed-form symmetric 3x3 solve.  Per view: 16 B pixel + 4 B camera index streamed, the camera record (Rt, t: 96 B = three
-// 256-bit loads) gathered from L1 / L2; the intrinsics record is re-read only when the camera MODEL changes between two views
-// of the point (one model per Camera datablock in the reference: almost never) -- the kernel is bound by load instructions /
-// L1 wavefronts, not by bytes.  24 B + 1 B out per point.  SURVEY 8(d) bytes: 72 B per view (pose + ray) + 24 B per point.
-// (Eight lanes per point with a shuffle tree was measured 2x slower: 3.6 ms vs 1.8 ms for 10.9 M points.)
+// closed-form symmetric 3x3 solve.  Per view: 16 B pixel + 4 B camera index streamed (both prefetched one view ahead), the
+// camera's DLT record gathered from L1 / L2: 64 B = two sectors {unit quaternion of Rt, Rt t} (k_dlt_records, once per call)
+// instead of the 96 B of {Rt, t}; Rt is rebuilt from the quaternion in registers.  NO division per view: the ray is
+// normalised by construction (dirFromUV.xy / dirFromUV.z, where z = f cancels) and the two reciprocals of the lens model
+// are taken once per camera MODEL (re-read only when the model changes between two views of the point: one model per
+// Camera datablock in the reference, almost never).  24 B + 1 B out per point.  SURVEY 8(d) bytes: 72 B per view (pose + ray)
+// + 24 B per point.  Round-2 steps on 2 M points / 10 M views (scripts/prof_dlt.py): 0.287 ms -> 0.243 (divisions) -> 0.203
+// (record) -> 0.194 (pixel prefetch).  (Eight lanes per point with a shuffle tree was 2x slower; the camera table in shared
+// memory and a 64-register cap were slower too.)
 // ---------------------------------------------------------------------------
+__global__ void k_dlt_records(DevProblem P) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P.Nc) return;
+    double cc[12], rec[8];
+#pragma unroll
+    for (int i = 0; i < 12; i++) cc[i] = P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i];
+    dlt_record(cc, rec);
+#pragma unroll
+    for (int i = 0; i < 8; i++) P.dlt_rec[8 * (size_t)c + i] = rec[i];
+}
+template <int EXP>   // EXP != 0: timing experiments only (1: every view reads camera 0's record; 2: every view reads pixel 0)
 __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points, const int32_t* __restrict__ view_off,
                                                      const int32_t* __restrict__ view_cam,
                                                      const double* __restrict__ view_uv, double* xyz_out,
@@ -223,29 +240,29 @@ __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points,
     double A[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
     const int k0 = __ldg(view_off + i), k1 = __ldg(view_off + i + 1);
     int model = -1;
-    double intr[10];
+    double intr[10], inv_f = 0.0, inv_fx = 0.0;   // the two reciprocals of the lens model: once per camera model, not per view
     int cam_next = k0 < k1 ? __ldg(view_cam + k0) : 0;
+    double2 uv_next = k0 < k1 ? ldg2(view_uv + 2 * (size_t)k0) : make_double2(0.0, 0.0);
     for (int k = k0; k < k1; k++) {
         const int cam = cam_next;
-        if (k + 1 < k1) cam_next = __ldg(view_cam + k + 1);   // next index in flight during this view's gathers
-        const double* cc = P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam;
-        double ccr[12];
-        {
-            const d4 c0 = ld256(cc), c1 = ld256(cc + 4), c2 = ld256(cc + 8);
-            ccr[0] = c0.x; ccr[1] = c0.y; ccr[2] = c0.z; ccr[3] = c0.w; ccr[4] = c1.x; ccr[5] = c1.y; ccr[6] = c1.z; ccr[7] = c1.w;
-            ccr[8] = c2.x; ccr[9] = c2.y; ccr[10] = c2.z; ccr[11] = c2.w;
+        const double2 uv = uv_next;
+        if (k + 1 < k1) {   // next index and pixel in flight during this view's gather and arithmetic
+            cam_next = __ldg(view_cam + k + 1);
+            uv_next = ldg2(view_uv + 2 * (size_t)(EXP == 2 ? ((k + 1) & 1) : k + 1));
         }
+        const double* rc = P.dlt_rec + 8 * (size_t)(EXP == 1 ? (cam & 1) : cam);
+        const d4 q = ld256(rc), cv = ld256(rc + 4);   // 64 bytes: two sectors
         const int m = __ldg(P.cam_model + cam);
         if (m != model) {
             model = m;
             const double* in = P.intr + 10 * m;
 #pragma unroll
             for (int j = 0; j < 5; j++) { const double2 v = ldg2(in + 2 * j); intr[2 * j] = v.x; intr[2 * j + 1] = v.y; }
+            inv_f = 1.0 / intr[0]; inv_fx = 1.0 / (intr[0] + intr[6]);
         }
-        const double2 uv = ldg2(view_uv + 2 * (size_t)k);
-        double d[3];
-        dir_from_uv(uv.x, uv.y, intr, d);
-        dlt_accumulate(ccr, d, A, b);
+        double x, y;   // dirFromUV.xy / dirFromUV.z: the factor f of the reference's ray cancels, no division per view
+        dir_from_uv_xy(uv.x, uv.y, intr, inv_f, inv_fx, &x, &y);
+        dlt_accumulate_rec(q.x, q.y, q.z, q.w, cv.x, cv.y, cv.z, x, y, A, b);
     }
     double Ai[6];
     const bool ok = inv3_sym(A, Ai);
@@ -261,7 +278,13 @@ __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points,
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st) {
     // (a variant with the camera table in shared memory, persistent 1024-thread blocks, was measured slower: 1.84 vs 1.49 ms)
-    if (n_points) k_triangulate<<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
+    const char* e = std::getenv("SBA_DLT_EXP");
+    const int ex = e ? std::atoi(e) : 0;
+    if (!n_points) return;
+    if (P.Nc) k_dlt_records<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);   // after the pose cache (the callers launch it first)
+    if (ex == 1) k_triangulate<1><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
+    else if (ex == 2) k_triangulate<2><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
+    else k_triangulate<0><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
 }
 
 }  // namespace sba

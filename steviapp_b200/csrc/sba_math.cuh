@@ -509,6 +509,72 @@ SBA_HD bool inv6_spd(const double* A, double* Ai) {
     return true;
 }
 
+// dirFromUV divided by its z component (= f): the normalised view ray (x, y, 1) the DLT needs, with the two reciprocals
+// 1 / f and 1 / (f + t1) supplied by the caller (per camera MODEL, not per view): no division per view.
+SBA_HD void dir_from_uv_xy(double u, double v, const double* in, double inv_f, double inv_fx, double* xo, double* yo) {
+    const double y = (v - in[2]) * inv_f;
+    const double x = (u - in[1] - in[7] * y) * inv_fx;
+    const double r2 = x * x + y * y;
+    const double rad = r2 * (in[3] + r2 * (in[4] + r2 * in[5]));
+    const double xy = x * y;
+    *xo = x + x * rad + 2.0 * xy * in[6] + (r2 + 2.0 * x * x) * in[7];
+    *yo = y + y * rad + (r2 + 2.0 * y * y) * in[6] + 2.0 * xy * in[7];
+}
+// DLT camera record: 8 doubles = the unit quaternion (w, x, y, z) of Rt (the world -> sensor rotation of the cache record) and
+// c = Rt t -- 64 bytes, two sectors per view instead of the three of {Rt, t}; the kernel rebuilds Rt from the quaternion
+// (18 flops) and no longer computes c per view.  Shepperd's branch on the largest of (trace, R00, R11, R22).
+SBA_HD void dlt_record(const double* cc, double* rec) {
+    const double m00 = cc[0], m01 = cc[1], m02 = cc[2], m10 = cc[3], m11 = cc[4], m12 = cc[5], m20 = cc[6], m21 = cc[7], m22 = cc[8];
+    const double tr = m00 + m11 + m22;
+    double w, x, y, z;
+    if (tr >= m00 && tr >= m11 && tr >= m22) {
+        const double s = 2.0 * sqrt(1.0 + tr);
+        w = 0.25 * s; x = (m21 - m12) / s; y = (m02 - m20) / s; z = (m10 - m01) / s;
+    } else if (m00 >= m11 && m00 >= m22) {
+        const double s = 2.0 * sqrt(1.0 + m00 - m11 - m22);
+        w = (m21 - m12) / s; x = 0.25 * s; y = (m01 + m10) / s; z = (m02 + m20) / s;
+    } else if (m11 >= m22) {
+        const double s = 2.0 * sqrt(1.0 + m11 - m00 - m22);
+        w = (m02 - m20) / s; x = (m01 + m10) / s; y = 0.25 * s; z = (m12 + m21) / s;
+    } else {
+        const double s = 2.0 * sqrt(1.0 + m22 - m00 - m11);
+        w = (m10 - m01) / s; x = (m02 + m20) / s; y = (m12 + m21) / s; z = 0.25 * s;
+    }
+    const double n = 1.0 / sqrt(w * w + x * x + y * y + z * z);
+    rec[0] = w * n; rec[1] = x * n; rec[2] = y * n; rec[3] = z * n;
+    rec[4] = m00 * cc[9] + m01 * cc[10] + m02 * cc[11];
+    rec[5] = m10 * cc[9] + m11 * cc[10] + m12 * cc[11];
+    rec[6] = m20 * cc[9] + m21 * cc[10] + m22 * cc[11];
+    rec[7] = 0.0;
+}
+// one DLT view from the record: rows of Rt rebuilt from the quaternion, ray normalised to (x, y, 1)
+SBA_HD void dlt_accumulate_rec(double qw, double qx, double qy, double qz, double c0, double c1, double c2, double x, double y, double* A,
+                               double* b) {
+    const double xx = qx * qx, yy = qy * qy, zz = qz * qz, xy = qx * qy, xz = qx * qz, yz = qy * qz, wx = qw * qx, wy = qw * qy, wz = qw * qz;
+    const double m00 = 1.0 - 2.0 * (yy + zz), m01 = 2.0 * (xy - wz), m02 = 2.0 * (xz + wy);
+    const double m10 = 2.0 * (xy + wz), m11 = 1.0 - 2.0 * (xx + zz), m12 = 2.0 * (yz - wx);
+    const double m20 = 2.0 * (xz - wy), m21 = 2.0 * (yz + wx), m22 = 1.0 - 2.0 * (xx + yy);
+    const double r0x = x * m20 - m00, r0y = x * m21 - m01, r0z = x * m22 - m02;
+    const double r1x = y * m20 - m10, r1y = y * m21 - m11, r1z = y * m22 - m12;
+    const double h0 = x * c2 - c0, h1 = y * c2 - c1;
+    b[0] += r0x * h0 + r1x * h1; b[1] += r0y * h0 + r1y * h1; b[2] += r0z * h0 + r1z * h1;
+    A[0] += r0x * r0x + r1x * r1x; A[1] += r0x * r0y + r1x * r1y; A[2] += r0x * r0z + r1x * r1z;
+    A[3] += r0y * r0y + r1y * r1y; A[4] += r0y * r0z + r1y * r1z; A[5] += r0z * r0z + r1z * r1z;
+}
+
+// dlt_accumulate for a ray already normalised to (x, y, 1)
+SBA_HD void dlt_accumulate_xy(const double* cc, double x, double y, double* A, double* b) {
+    const double c0 = cc[0] * cc[9] + cc[1] * cc[10] + cc[2] * cc[11];
+    const double c1 = cc[3] * cc[9] + cc[4] * cc[10] + cc[5] * cc[11];
+    const double c2 = cc[6] * cc[9] + cc[7] * cc[10] + cc[8] * cc[11];
+    const double r0x = x * cc[6] - cc[0], r0y = x * cc[7] - cc[1], r0z = x * cc[8] - cc[2];
+    const double r1x = y * cc[6] - cc[3], r1y = y * cc[7] - cc[4], r1z = y * cc[8] - cc[5];
+    const double h0 = x * c2 - c0, h1 = y * c2 - c1;
+    b[0] += r0x * h0 + r1x * h1; b[1] += r0y * h0 + r1y * h1; b[2] += r0z * h0 + r1z * h1;
+    A[0] += r0x * r0x + r1x * r1x; A[1] += r0x * r0y + r1x * r1y; A[2] += r0x * r0z + r1x * r1z;
+    A[3] += r0y * r0y + r1y * r1y; A[4] += r0y * r0z + r1y * r1z; A[5] += r0z * r0z + r1z * r1z;
+}
+
 // One DLT view: accumulates the inhomogeneous normal equations of the two rows
 //   (x r3 - r1) . X = x c3 - c1,  (y r3 - r2) . X = y c3 - c2
 // (r_i rows of R^T, c = R^T t, (x,y) = dirFromUV.xy / dir.z).  A packed sym 3x3.

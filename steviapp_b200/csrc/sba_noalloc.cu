@@ -3,9 +3,9 @@
 // run's operators.  Same kernels as sba_triangulate (K0 pose cache + K5 k_triangulate); what differs is where their scratch
 // lives: sba_triangulate keeps the camera cache in the handle's arena (cudaMalloc at finalize) and stages its arguments in
 // cudaMalloc'ed buffers, here every intermediate sits in ONE file-scope device array of fixed size:
-//     camera cache (24 doubles per camera), Q block (12 per camera), the sanitised camera-model index per camera,
+//     camera cache (24 doubles per camera), Q block (12 per camera), DLT record (8 per camera), the sanitised camera-model index per camera,
 //     the clamped view offsets, the sanitised camera index of every view, one "bad input" flag per point.
-// Every GPU that loads the library holds the array (SBA_NOALLOC_SCRATCH_BYTES = 6.5 MiB) until the process exits.
+// Every GPU that loads the library holds the array (SBA_NOALLOC_SCRATCH_BYTES = 6.75 MiB) until the process exits.
 //
 // The array's name is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, once per device,
 // with that device current (noalloc_scratch below).  All calls on a device share the array and it keeps the previous call's
@@ -24,7 +24,8 @@ namespace {
 constexpr size_t align256(size_t b) { return (b + 255) / 256 * 256; }
 constexpr size_t NA_OFF_CACHE = 0;
 constexpr size_t NA_OFF_Q = NA_OFF_CACHE + align256(sizeof(double) * CAM_CACHE_STRIDE * SBA_NOALLOC_MAX_CAMS);
-constexpr size_t NA_OFF_MODEL = NA_OFF_Q + align256(sizeof(double) * 12 * SBA_NOALLOC_MAX_CAMS);
+constexpr size_t NA_OFF_REC = NA_OFF_Q + align256(sizeof(double) * 12 * SBA_NOALLOC_MAX_CAMS);
+constexpr size_t NA_OFF_MODEL = NA_OFF_REC + align256(sizeof(double) * 8 * SBA_NOALLOC_MAX_CAMS);
 constexpr size_t NA_OFF_VOFF = NA_OFF_MODEL + align256(sizeof(int32_t) * SBA_NOALLOC_MAX_CAMS);
 constexpr size_t NA_OFF_VCAM = NA_OFF_VOFF + align256(sizeof(int32_t) * ((size_t)SBA_NOALLOC_MAX_POINTS + 1));
 constexpr size_t NA_OFF_BAD = NA_OFF_VCAM + align256(sizeof(int32_t) * (size_t)SBA_NOALLOC_MAX_VIEWS);
@@ -123,6 +124,7 @@ int triangulate_noalloc(int32_t n_cams, const double* raxis, const double* t, co
     P.cam_model = model_s;
     P.cam_cache = reinterpret_cast<double*>(base + NA_OFF_CACHE);
     P.cam_Q = reinterpret_cast<double*>(base + NA_OFF_Q);
+    P.dlt_rec = reinterpret_cast<double*>(base + NA_OFF_REC);
     if (n_cams) {
         k_na_models<<<cdiv(n_cams, 256), 256, 0, st>>>(n_cams, n_models, cam_model, model_s);
         launch_pose_cache(P, st);
