@@ -109,6 +109,7 @@ struct DevProblem {
     int32_t* ex_fold_off; // offsets (doubles, relative to ex_row) of the partial vectors of every camera tile, fixed order
     double* cam_Q;        // 12*Nc: Q = (R Jr)^T row-major (9) + pad, written by K0: C = A [X - t]x Q^T
     double* dlt_rec;      // 8*Nc: quaternion of Rt + Rt t per camera, written by launch_triangulate for its kernel (sba_math.cuh dlt_record)
+    double* intr_r;       // 2*Nm: 1 / f and 1 / (f + t1) of every camera model, refreshed with the pose cache (k_intr_recip)
     // ---- peer-memory all-reduce of the PCG operator partial (multi-GPU; sba_kernels_pcg.cu, PM_XCHG) ----
     // every rank owns a mailbox, mapped into every process (CUDA IPC, stores travel over NVLink / NVSwitch):
     //   double   data[2][xchg_n][xchg_stride]     (parity of the exchange number, source rank, vector element)

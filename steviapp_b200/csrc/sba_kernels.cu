@@ -84,7 +84,15 @@ __global__ void k_pose_cache(DevProblem P) {
 #pragma unroll
     for (int i = 0; i < CAM_CACHE_STRIDE; i++) P.cam_cache[(size_t)CAM_CACHE_STRIDE * c + i] = out[i];
 }
+__global__ void k_intr_recip(DevProblem P) {
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= P.Nm) return;
+    const double f = P.intr[10 * (size_t)m], t1 = P.intr[10 * (size_t)m + 6];
+    P.intr_r[2 * (size_t)m] = 1.0 / f;
+    P.intr_r[2 * (size_t)m + 1] = 1.0 / (f + t1);
+}
 void launch_pose_cache(const DevProblem& P, cudaStream_t st) {
+    if (P.Nm && P.intr_r) k_intr_recip<<<cdiv(P.Nm, 128), 128, 0, st>>>(P);
     if (P.Nmt) k_mount_cache<<<cdiv(P.Nmt, 128), 128, 0, st>>>(P);
     k_pose_cache<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);
 }
@@ -105,7 +113,7 @@ template <bool JAC, bool INFO>
 __device__ __forceinline__ void k1_slot(const DevProblem& P, const double* cc, const double* intr, int spherical, size_t Ns, int s,
                                         double2 uv, const double (&X)[3], double& acc, int& bad) {
     double d[3];
-    dir_from_uv(uv.x, uv.y, intr, d);
+    dir_from_uv_r(uv.x, uv.y, intr, intr[10], intr[11], d);
     double W[4] = {1.0, 0.0, 0.0, 1.0};
     if (INFO) {
 #pragma unroll
@@ -142,7 +150,7 @@ __device__ __forceinline__ void k1_slot(const DevProblem& P, const double* cc, c
 // (ncu r2f: FP64 pipe 20 %, DRAM 46 %, 42 % warps active), not by bytes or flops.
 template <bool JAC, bool PIPE, int MINB, bool INFO>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB) k_residual_jacobian(DevProblem P) {
-    __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD];
+    __shared__ double s_cam[WARPS_PER_BLOCK][CAM_CACHE_STRIDE + SBA_INTR_PAD + 2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x * WARPS_PER_BLOCK + warp;
     if (tile >= P.Nt) return;
@@ -150,7 +158,11 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32, MINB) k_residual_jacobia
     const int start = __ldg(P.tile_start + tile), len = __ldg(P.tile_len + tile);
     double* cc = s_cam[warp];
     if (lane < CAM_CACHE_STRIDE) cc[lane] = __ldg(P.cam_cache + (size_t)CAM_CACHE_STRIDE * cam + lane);
-    if (lane < 10) cc[CAM_CACHE_STRIDE + lane] = __ldg(P.intr + 10 * __ldg(P.cam_model + cam) + lane);
+    {
+        const int m = __ldg(P.cam_model + cam);
+        if (lane < 10) cc[CAM_CACHE_STRIDE + lane] = __ldg(P.intr + 10 * m + lane);
+        else if (lane < 12) cc[CAM_CACHE_STRIDE + lane] = __ldg(P.intr_r + 2 * m + (lane - 10));   // 1 / f, 1 / (f + t1)
+    }
     __syncwarp();
     const double* intr = cc + CAM_CACHE_STRIDE;
     const int spherical = P.cam_kind[cam];

@@ -73,13 +73,15 @@ __device__ __forceinline__ void linearize_slot(const DevProblem& P, int q, int l
         crec(cam, ccr);
 #pragma unroll
         for (int i = 12; i < 22; i++) ccr[i] = 0.0;
-        const double* in = P.intr + 10 * (P.Nm == 1 ? 0 : __ldg(P.cam_model + cam));
+        const int mdl = P.Nm == 1 ? 0 : __ldg(P.cam_model + cam);
+        const double* in = P.intr + 10 * mdl;
         double intr[10];
 #pragma unroll
         for (int i = 0; i < 5; i++) { const double2 t = ldg2(in + 2 * i); intr[2 * i] = t.x; intr[2 * i + 1] = t.y; }
+        const double2 rcp = ldg2(P.intr_r + 2 * mdl);   // 1 / f, 1 / (f + t1): the same table K1 reads (bitwise equal A and res)
         const double2 uv = ldcs2(P.q_uv + 2 * (size_t)q);
         double d[3];
-        dir_from_uv(uv.x, uv.y, intr, d);
+        dir_from_uv_r(uv.x, uv.y, intr, rcp.x, rcp.y, d);
         double W[4];
         const double* Wp = nullptr;
         if (P.q_info) {

@@ -96,6 +96,23 @@ SBA_HD void dir_from_uv(double u, double v, const double* in, double* d) {
     d[2] = f;
 }
 
+// The same ray with the two reciprocals of the lens model, 1 / f and 1 / (f + t1), supplied by the caller (table intr_r, once per
+// camera model and linearisation: k_intr_recip): no division per observation in K1 / K1c / K1p.  K1 and K1p both use THIS form, so the
+// camera-order and point-order copies of A and res stay bitwise identical; against dir_from_uv it differs by rounding only.
+SBA_HD void dir_from_uv_r(double u, double v, const double* in, double inv_f, double inv_fx, double* d) {
+    const double f = in[0];
+    const double y = (v - in[2]) * inv_f;
+    const double x = (u - in[1] - in[7] * y) * inv_fx;
+    const double r2 = x * x + y * y;
+    const double rad = r2 * (in[3] + r2 * (in[4] + r2 * in[5]));
+    const double xy = x * y;
+    const double dtx = 2.0 * xy * in[6] + (r2 + 2.0 * x * x) * in[7];
+    const double dty = (r2 + 2.0 * y * y) * in[6] + 2.0 * xy * in[7];
+    d[0] = (x + x * rad + dtx) * f;
+    d[1] = (y + y * rad + dty) * f;
+    d[2] = f;
+}
+
 // dirFromUV and its Jacobian with respect to (f, ppx, ppy, k1, k2, k3, t1, t2): dd[8 r + c] = d d_r / d intr_c, r = x, y, z
 // (d_z = f).  Same expressions as in obs_intr_jac_pbar below.
 SBA_HD void dir_from_uv_jac(double u, double v, const double* in, double* d, double* dd) {
