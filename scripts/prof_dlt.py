@@ -16,8 +16,3 @@ s = SBASolver()
 synthetic.load_into(s, sc)
 x, ok, ms = s.triangulate(view_off, view_cam, view_uv)
 print(view_off.size - 1, "points", ms, "ms", float(ok.mean()))
-for ex in os.environ.get("SBA_DLT_EXP_LIST", "").split(","):   # timing experiments (results are garbage for ex != 0)
-    if ex:
-        os.environ["SBA_DLT_EXP"] = ex
-        t = min(s.triangulate(view_off, view_cam, view_uv)[2] for _ in range(3))
-        print("experiment", ex, "kernel ms %.4f" % t, "per point ns %.3f" % (1e6 * t / (view_off.size - 1)))

@@ -230,7 +230,6 @@ __global__ void k_dlt_records(DevProblem P) {
 #pragma unroll
     for (int i = 0; i < 8; i++) P.dlt_rec[8 * (size_t)c + i] = rec[i];
 }
-template <int EXP>   // EXP != 0: timing experiments only (1: every view reads camera 0's record; 2: every view reads pixel 0)
 __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points, const int32_t* __restrict__ view_off,
                                                      const int32_t* __restrict__ view_cam,
                                                      const double* __restrict__ view_uv, double* xyz_out,
@@ -248,9 +247,9 @@ __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points,
         const double2 uv = uv_next;
         if (k + 1 < k1) {   // next index and pixel in flight during this view's gather and arithmetic
             cam_next = __ldg(view_cam + k + 1);
-            uv_next = ldg2(view_uv + 2 * (size_t)(EXP == 2 ? ((k + 1) & 1) : k + 1));
+            uv_next = ldg2(view_uv + 2 * (size_t)(k + 1));
         }
-        const double* rc = P.dlt_rec + 8 * (size_t)(EXP == 1 ? (cam & 1) : cam);
+        const double* rc = P.dlt_rec + 8 * (size_t)cam;
         const d4 q = ld256(rc), cv = ld256(rc + 4);   // 64 bytes: two sectors
         const int m = __ldg(P.cam_model + cam);
         if (m != model) {
@@ -278,13 +277,9 @@ __global__ void __launch_bounds__(256) k_triangulate(DevProblem P, int n_points,
 void launch_triangulate(const DevProblem& P, int n_points, const int32_t* view_off, const int32_t* view_cam,
                         const double* view_uv, double* xyz_out, uint8_t* ok_out, cudaStream_t st) {
     // (a variant with the camera table in shared memory, persistent 1024-thread blocks, was measured slower: 1.84 vs 1.49 ms)
-    const char* e = std::getenv("SBA_DLT_EXP");
-    const int ex = e ? std::atoi(e) : 0;
     if (!n_points) return;
     if (P.Nc) k_dlt_records<<<cdiv(P.Nc, 128), 128, 0, st>>>(P);   // after the pose cache (the callers launch it first)
-    if (ex == 1) k_triangulate<1><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
-    else if (ex == 2) k_triangulate<2><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
-    else k_triangulate<0><<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
+    k_triangulate<<<cdiv(n_points, 256), 256, 0, st>>>(P, n_points, view_off, view_cam, view_uv, xyz_out, ok_out);
 }
 
 }  // namespace sba
