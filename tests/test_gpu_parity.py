@@ -356,6 +356,28 @@ def test_block_sparse_panels_match_dense_tiles(case, monkeypatch):
         assert abs(x - y) <= 1e-10 * max(y, 1.0)
 
 
+def test_direct_panel_assembly_equals_the_two_pass_build(monkeypatch):
+    """Direct mode (the assembly writes the panels itself, SBA_EX_DIRECT, default on with the panels on one GPU) against the
+    dense-tile build + compaction: bitwise equal LM, and the dense tiles the hooks read (refreshed on demand from the panels)
+    equal to the ones the two-pass build wrote."""
+    sc = synthetic.make_scene(None, n_cams=300, n_pts=30000, n_obs=150000, seed=7)
+    monkeypatch.setenv("SBA_PS_SPARSE", "1")
+    out, tiles, mv = {}, {}, {}
+    rng = np.random.default_rng(5)
+    x = rng.normal(size=(sc["n_cams"], 6)); x[0] = 0.0     # zero at the fixed camera
+    lam_c = rng.uniform(0.5, 2.0, (sc["n_cams"], 6)); lam_p = rng.uniform(0.5, 2.0, (sc["n_pts"], 3))
+    for direct in ("1", "0"):
+        monkeypatch.setenv("SBA_EX_DIRECT", direct)
+        s, _ = gpu_solver(sc, operator_mode=3)
+        out[direct] = s.solve(max_iterations=3, **FIXED_ITERS)
+        tiles[direct] = s.explicit_dense()
+        mv[direct] = s.schur_matvec(lam_c, lam_p, x)      # its own build with these diagonals, then the tile mat-vec
+        s.close()
+    assert out["1"]["cost_history"] == out["0"]["cost_history"] and out["1"]["pcg_iters_history"] == out["0"]["pcg_iters_history"]
+    assert np.array_equal(tiles["1"][0], tiles["0"][0]) and np.array_equal(tiles["1"][1], tiles["0"][1])
+    assert np.array_equal(mv["1"][0], mv["0"][0]) and np.array_equal(mv["1"][1], mv["0"][1])
+
+
 def test_persistent_pcg_iteration_cap_and_rerun():
     """The kernel stops at the iteration cap like the sequential loop, and is bitwise reproducible."""
     sc = synthetic.make_scene("ladybug")
