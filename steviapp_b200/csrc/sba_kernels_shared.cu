@@ -77,17 +77,21 @@ __device__ __forceinline__ void block_reduce_store(double (&v)[N], double* part,
 // ---------------------------------------------------------------------------
 // per linearisation, point order: W_g per point, partial sums of G^T G (36 packed) and G^T res (8)
 // ---------------------------------------------------------------------------
+// Persistent grid (round 2): a thread walks its slots with a grid stride and keeps the 44 sums of G^T G | G^T res in registers
+// across them; the block tree runs ONCE per block at the end (it was once per 256 slots: 220 double shuffles per warp and 21 000
+// block partials for a single-block fold on the Venice shape).  Fixed slot -> thread assignment: deterministic.
 __global__ void __launch_bounds__(256) k_shared_points(DevProblem P, int g, int kind) {
     __shared__ double sm[8][SH_RED];
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;   // Nq % 32 == 0, grid covers whole warps; threads past Nq idle
     const int lane = threadIdx.x & 31;
-    const bool in_range = q < P.Nq;
-    const int pt = in_range ? __ldcs(P.q_pt + q) : -1;
-    double v[24], hg[44];
-#pragma unroll
-    for (int i = 0; i < 24; i++) v[i] = 0.0;
+    double hg[44];
 #pragma unroll
     for (int i = 0; i < 44; i++) hg[i] = 0.0;
+    // Nq % 32 == 0 and the stride is a multiple of 32: the lanes of a warp stay together (the shuffles below need that)
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < P.Nq; q += gridDim.x * blockDim.x) {
+    const int pt = __ldcs(P.q_pt + q);
+    double v[24];
+#pragma unroll
+    for (int i = 0; i < 24; i++) v[i] = 0.0;
     if (pt >= 0) {
         const int cam = __ldcs(P.q_cam + q);
         if (__ldg(P.cam_grp + 2 * cam + kind) == g) {
@@ -128,9 +132,9 @@ __global__ void __launch_bounds__(256) k_shared_points(DevProblem P, int g, int 
 #pragma unroll
                 for (int c1 = 0; c1 < 8; c1++)
 #pragma unroll
-                    for (int c2 = c1; c2 < 8; c2++) hg[k++] = G[c1] * G[c2] + G[8 + c1] * G[8 + c2];
+                    for (int c2 = c1; c2 < 8; c2++) hg[k++] += G[c1] * G[c2] + G[8 + c1] * G[8 + c2];
 #pragma unroll
-                for (int c = 0; c < 8; c++) hg[36 + c] = G[c] * r[0] + G[8 + c] * r[1];
+                for (int c = 0; c < 8; c++) hg[36 + c] += G[c] * r[0] + G[8 + c] * r[1];
             }
         }
     }
@@ -152,6 +156,7 @@ __global__ void __launch_bounds__(256) k_shared_points(DevProblem P, int g, int 
 #pragma unroll
         for (int i = 0; i < 24; i += 4) st256(o + i, v[i], v[i + 1], v[i + 2], v[i + 3]);
     }
+    }   // slots of this thread
     block_reduce_store<44>(hg, P.sh_part, sm);
 }
 __global__ void k_shared_points_heavy(DevProblem P, int g) {
@@ -234,9 +239,10 @@ void launch_shared_linearize(const DevProblem& P, cudaStream_t st) {
     if (!P.Nq) return;
     const int nb = cdiv(P.Nq, 256);
     for (int g = 0; g < P.Ng; g++) {
-        k_shared_points<<<nb, 256, 0, st>>>(P, g, P.grp_kind[g]);
+        const int nbp = std::min(nb, 148 * 4);   // persistent: a few blocks per SM, every thread walks its slots
+        k_shared_points<<<nbp, 256, 0, st>>>(P, g, P.grp_kind[g]);
         if (P.Nh) k_shared_points_heavy<<<cdiv(P.Nh, 128), 128, 0, st>>>(P, g);
-        k_shared_fold_hg<<<1, RED_BLOCK, 0, st>>>(P, g, nb);
+        k_shared_fold_hg<<<1, RED_BLOCK, 0, st>>>(P, g, nbp);
     }
     if (P.cam_mount) {
         for (int gm = 0; gm < P.Ng; gm++)
