@@ -577,16 +577,22 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) k_shared_gd(DevProblem P
     const size_t Ns = (size_t)P.Ns;
     const int gk[2] = {__ldg(P.cam_grp + 2 * cam), __ldg(P.cam_grp + 2 * cam + 1)};
     double d8[2][8];
-    for (int k = 0; k < 2; k++) if (gk[k] >= 0) grp_delta(P, x, gk[k], d8[k]);
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) d8[k][c] = 0.0;
+        if (gk[k] >= 0) grp_delta(P, x, gk[k], d8[k]);
+    }
     for (int s = start + lane; s < start + len; s += 32) {
         double m0 = 0.0, m1 = 0.0;
         if (__ldcs(P.obs_pt + s) >= 0) {
-            const double p0 = P.Pc[s], p1 = P.Pc[Ns + s], p2 = P.Pc[2 * Ns + s];
+            const double p0 = __ldcs(P.Pc + s), p1 = __ldcs(P.Pc + Ns + s), p2 = __ldcs(P.Pc + 2 * Ns + s);
             const double2 uv = ldcs2(P.obs_uv + 2 * (size_t)s);
             double W[4];
             const double* Wp = nullptr;
             if (P.obs_info) { for (int i = 0; i < 4; i++) W[i] = P.obs_info[i * Ns + s]; Wp = W; }
-            for (int k = 0; k < 2; k++) {
+#pragma unroll
+            for (int k = 0; k < 2; k++) {   // unrolled: the group kind is a compile-time constant inside, d8 stays in registers
                 if (gk[k] < 0) continue;
                 double G[16];
                 shared_jac(P, gk[k], k, cam, p0, p1, p2, uv.x, uv.y, Wp, G);
